@@ -1,0 +1,99 @@
+/*
+ * pirl_rcwa.h -- C ABI of the B200-native batched RCWA backend for DeflectorGym.
+ *
+ * This is the drop-in boundary for ONE path of the reference
+ * (jLabKAIST/Physics-Informed-Reinforcement-Learning): the per-step physics call
+ *
+ *     MeentBase.get_efficiency(struct)        deflector-gym/deflector_gym/envs/meent_env.py:26-46
+ *       -> JLABCode(...).reproduce_acs_cell   deflector-gym/third_party/meent/JLAB/solver.py:16-38
+ *       -> to_conv_mat (x2)                   .../meent/on_numpy/convolution_matrix.py:89-114
+ *       -> RCWALight.solve -> solve_1d (TM)   .../meent/on_numpy/rcwa.py:21-34, _base.py:119-180
+ *       -> transfer_1d_1/2/3                  .../meent/on_numpy/transfer_method.py:4-75
+ *
+ * and the discrete env transition around it (DeflectorBase.flip, base.py:37-42;
+ * MeentIndex.step, meent_env.py:90-99).  Everything is plain C: pointers, sizes, no
+ * torch / C++ types.  All functions return 0 on success, <0 for an argument error,
+ * >0 for a CUDA runtime error code; pirl_last_error() returns a description.
+ * No exception crosses this boundary.  There is NO CPU fallback: if no CUDA device
+ * is usable, pirl_rcwa_create fails.
+ */
+#ifndef PIRL_RCWA_H
+#define PIRL_RCWA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIRL_ABI_VERSION 1
+
+/* status bits reported per structure (0 == ok) */
+#define PIRL_ST_EIG_NOT_CONVERGED 1  /* QL iteration cap / rotation buffer exceeded          */
+#define PIRL_ST_NONFINITE 2          /* a non-finite efficiency was produced                 */
+#define PIRL_ST_NOT_POSDEF 4         /* permittivity Toeplitz matrices not positive definite */
+
+/* Constants the reference hard-codes per env (meent_env.py:36-44, base.py:16-20). */
+typedef struct pirl_cfg {
+  int32_t n_cells;     /* pixels per period (256 / 512)                                  */
+  int32_t order;       /* Fourier order N; ff = 2N+1 harmonics                            */
+  double n_inc;        /* n_I  = 1.45  (incidence medium)                                 */
+  double n_exit;       /* n_II = 1.0                                                      */
+  double n_groove;     /* 1.0                                                             */
+  double theta_deg;    /* incidence angle; only 0 is supported (as DeflectorGym uses)     */
+  int32_t pol;         /* 1 = TM (the only polarisation on this path)                     */
+  int32_t max_batch;   /* structures processed per internal chunk (workspace sizing)      */
+  int32_t device;      /* CUDA device ordinal                                             */
+  int32_t reserved;
+} pirl_cfg;
+
+typedef struct pirl_handle pirl_handle;
+
+int pirl_abi_version(void);
+const char* pirl_last_error(void);
+
+/* Replaces RCWALight.__init__/_BaseRCWA.__init__ (rcwa.py:9-18, _base.py:81-117): allocates all
+ * device workspaces and tables once (the reference re-reads its material tables every call). */
+int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out);
+int pirl_rcwa_destroy(pirl_handle* h);
+
+/* Batched get_efficiency.  Replaces meent_env.py:26-46 + solver.py:16-38 for B structures.
+ *   patterns   device, int8 [B][n_cells], values +1 / -1 (anything > 0 counts as ridge)
+ *   params     device, double [B][4] or [1][4]: {wavelength_nm, deflection_angle_deg, thickness_nm, n_ridge}
+ *              (n_ridge = host-interpolated n_Si(lambda), convolution_matrix.py:40-52)
+ *   param_stride  4 for per-structure rows, 0 to broadcast row 0
+ *   eff        device, double [B]      = de_ti[N-1]           (solver.py:38)
+ *   de_r3      device, double [B][3] or NULL: de_ri[N-1], de_ri[N], de_ri[N+1]
+ *   de_t3      device, double [B][3] or NULL: de_ti[N-1], de_ti[N], de_ti[N+1]
+ *   status     device, int32 [B] or NULL
+ *   stream     cudaStream_t (as void*); work is enqueued asynchronously, no host<->device copies.
+ */
+int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                   int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status, void* stream);
+
+/* Same call with HOST buffers (pinned or pageable): H2D of patterns/params, eval, D2H of results,
+ * synchronous.  This is the entry point a ctypes binding inside MeentBase.get_efficiency uses. */
+int pirl_rcwa_eval_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                        int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status);
+
+/* DeflectorBase.flip for B envs (base.py:37-42): patterns[b][a] = -patterns[b][a] iff 0 <= a <= n_cells-1. */
+int pirl_env_flip(int8_t* patterns, const int64_t* actions, int64_t B, int32_t n_cells, void* stream);
+
+/* MeentIndex.step bookkeeping (meent_env.py:90-99): reward = eff_new - eff_prev (this order, float64),
+ * eff_prev <- eff_new, best tracking as BestRecorder (wrappers.py:10-16: strict >). best_* may be NULL. */
+int pirl_env_reward(const double* eff_new, double* eff_prev, double* reward, double* best_eff,
+                    int8_t* best_patterns, const int8_t* patterns, int64_t B, int32_t n_cells, void* stream);
+
+/* Number of kernels this library launched since the handle was created (bench.py's gpu_launches). */
+int64_t pirl_rcwa_launch_count(pirl_handle* h);
+
+/* Test hook: copy a stage intermediate of the LAST chunk evaluated to a host buffer.
+ * what: 0 = reduced standard-form matrix C [B][ff][ff], 1 = tridiagonal d,e [B][2][ff],
+ *       2 = eigenvalues [B][ff], 3 = modes W (A-orthonormal, real basis) [B][ff][ff],
+ *       4 = rotation counts int64-as-double [B]                                               */
+int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, int64_t max_elems);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIRL_RCWA_H */

@@ -1,0 +1,327 @@
+// rcwa_api.cu -- C ABI (include/pirl_rcwa.h) over the kernels in rcwa_kernels.cuh.
+// Host side only owns: the handle, its device workspaces and two tiny tables.  No torch, no C++ types
+// in the exported signatures.
+#include "rcwa_kernels.cuh"
+#include "../../include/pirl_rcwa.h"
+
+#include <complex>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CUDA_TRY(expr)                                                                                 \
+  do {                                                                                                 \
+    cudaError_t _e = (expr);                                                                           \
+    if (_e != cudaSuccess)                                                                             \
+      return fail((int)_e, std::string(#expr) + ": " + cudaGetErrorString(_e));                        \
+  } while (0)
+
+struct pirl_handle {
+  pirl_cfg cfg;
+  int ff, ld, maxrot, sm_count;
+  size_t smem_optin;
+  // tables
+  cplx* d_tw = nullptr;
+  cplx* d_Dk = nullptr;
+  // chunk workspaces
+  double *Cbuf = nullptr, *Lbuf = nullptr, *Wbuf = nullptr, *tri = nullptr, *lam = nullptr;
+  cplx* rot_cs = nullptr;
+  uint8_t* rot_col = nullptr;
+  int *nrot = nullptr, *wstatus = nullptr;
+  double* scratch = nullptr;
+  size_t scratch_stride = 0;
+  int scratch_ctas = 0;
+  // launch plans
+  int front_grid, front_mats; size_t front_smem;
+  int tri_grid, tri_mats; size_t tri_smem;
+  int tail_grid, tail_mats; size_t tail_smem;
+  int apply_rows; size_t apply_smem;
+  size_t ql_smem;
+  int last_chunk = 0;
+  long long launches = 0;
+  // host staging for eval_host
+  int8_t* hd_patterns = nullptr; double* hd_params = nullptr; double* hd_out = nullptr; int32_t* hd_status = nullptr;
+  int64_t hd_cap = 0;
+  cudaStream_t own_stream = nullptr;
+};
+
+extern "C" int pirl_abi_version(void) { return PIRL_ABI_VERSION; }
+extern "C" const char* pirl_last_error(void) { return g_err.c_str(); }
+
+static constexpr int FRONT_NT = 256;
+static constexpr int TRI_NT = 256;
+static constexpr int TAIL_NT = 512;
+
+template <typename T>
+static cudaError_t dmalloc(T** p, size_t n) { return cudaMalloc((void**)p, n * sizeof(T)); }
+
+// how many matrices of `mat_bytes` fit beside `vec_bytes` in `budget` (capped at want)
+static int mats_that_fit(size_t budget, size_t vec_bytes, size_t mat_bytes, int want) {
+  int k = 0;
+  while (k < want && vec_bytes + (size_t)(k + 1) * mat_bytes <= budget) ++k;
+  return k;
+}
+
+extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
+  if (!cfg || !out) return fail(-1, "null argument");
+  if (cfg->order < 1 || cfg->order > 126) return fail(-2, "order must be in [1,126] (rotation column index is 8 bit)");
+  if (cfg->n_cells < 2 || cfg->n_cells > 65536) return fail(-3, "n_cells out of range");
+  if (cfg->pol != 1) return fail(-4, "only TM (pol=1) is implemented: it is the only polarisation DeflectorGym evaluates");
+  if (cfg->theta_deg != 0.0) return fail(-5, "only normal incidence (theta=0) is implemented (real-symmetric formulation)");
+  if (cfg->max_batch < 1) return fail(-6, "max_batch must be >= 1");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(e == cudaSuccess ? -7 : (int)e, "no CUDA device: this library has no CPU fallback");
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(-8, "bad device ordinal");
+  CUDA_TRY(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, cfg->device));
+
+  pirl_handle* h = new pirl_handle();
+  h->cfg = *cfg;
+  const int N = cfg->order, ff = 2 * N + 1, nc = cfg->n_cells;
+  h->ff = ff;
+  h->ld = ff;  // ff is odd -> column walks are bank-conflict free
+  h->maxrot = 3 * ff * ff;
+  h->sm_count = prop.multiProcessorCount;
+  h->smem_optin = prop.sharedMemPerBlockOptin;
+
+  // ---- tables (host, long double) ----
+  {
+    std::vector<cplx> tw(nc), Dk(2 * N + 1);
+    const long double PI = 3.141592653589793238462643383279502884L;
+    for (int p = 0; p < nc; ++p) {
+      long double a = -2.0L * PI * p / nc;
+      tw[p] = make_double2((double)cosl(a), (double)sinl(a));
+    }
+    const long double R = 4.0L * N + 2.0L, M = R * nc;
+    for (int k = 0; k <= 2 * N; ++k) {
+      std::complex<long double> d(1.0L, 0.0L);
+      if (k % nc != 0) {
+        std::complex<long double> num = 1.0L - std::polar(1.0L, -2.0L * PI * k / nc);
+        std::complex<long double> den = R * (1.0L - std::polar(1.0L, -2.0L * PI * k / M));
+        d = num / den;
+      }
+      d /= (long double)nc;
+      Dk[k] = make_double2((double)d.real(), (double)d.imag());
+    }
+    CUDA_TRY(dmalloc(&h->d_tw, nc));
+    CUDA_TRY(dmalloc(&h->d_Dk, 2 * N + 1));
+    CUDA_TRY(cudaMemcpy(h->d_tw, tw.data(), nc * sizeof(cplx), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(h->d_Dk, Dk.data(), (2 * N + 1) * sizeof(cplx), cudaMemcpyHostToDevice));
+  }
+  // ---- chunk workspaces ----
+  const size_t Bc = cfg->max_batch, m2 = (size_t)ff * ff;
+  CUDA_TRY(dmalloc(&h->Cbuf, Bc * m2));
+  CUDA_TRY(dmalloc(&h->Lbuf, Bc * m2));
+  CUDA_TRY(dmalloc(&h->Wbuf, Bc * m2));
+  CUDA_TRY(dmalloc(&h->tri, Bc * 2 * ff));
+  CUDA_TRY(dmalloc(&h->lam, Bc * ff));
+  CUDA_TRY(dmalloc(&h->rot_cs, Bc * h->maxrot));
+  CUDA_TRY(dmalloc(&h->rot_col, Bc * h->maxrot));
+  CUDA_TRY(dmalloc(&h->nrot, Bc));
+  CUDA_TRY(dmalloc(&h->wstatus, Bc));
+
+  // ---- launch plans: matrices go to shared memory when they fit, else to a per-CTA L2-resident spill ----
+  const size_t budget = h->smem_optin;
+  const size_t rmat = (size_t)ff * h->ld * sizeof(double), cmat = 2 * rmat;
+  {
+    size_t vec = (size_t)front_vec_doubles(ff, N, nc) * 8;
+    h->front_mats = mats_that_fit(budget, vec, rmat, 2);
+    h->front_smem = vec + h->front_mats * rmat;
+    int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / FRONT_NT, budget / std::max<size_t>(h->front_smem + 1024, 1)));
+    h->front_grid = h->sm_count * per_sm;
+    CUDA_TRY(cudaFuncSetAttribute(k_front<FRONT_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->front_smem));
+  }
+  {
+    size_t vec = (size_t)tridiag_vec_doubles(ff) * 8;
+    h->tri_mats = mats_that_fit(budget, vec, rmat, 2);
+    h->tri_smem = vec + h->tri_mats * rmat;
+    int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / TRI_NT, budget / std::max<size_t>(h->tri_smem + 1024, 1)));
+    h->tri_grid = h->sm_count * per_sm;
+    CUDA_TRY(cudaFuncSetAttribute(k_tridiag<TRI_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tri_smem));
+  }
+  {
+    size_t vec = (size_t)tail_vec_doubles(ff) * 8;
+    h->tail_mats = mats_that_fit(budget, vec, cmat, 2);
+    h->tail_smem = vec + h->tail_mats * cmat;
+    int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / TAIL_NT, budget / std::max<size_t>(h->tail_smem + 1024, 1)));
+    h->tail_grid = h->sm_count * per_sm;
+    if (ff <= 96) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem));
+    else if (ff <= 128) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem));
+    else CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem));
+  }
+  {
+    h->apply_rows = (ff <= 96) ? 96 : 64;
+    h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + (size_t)h->apply_rows * h->ld) * 8;
+    if (h->apply_smem > budget) { h->apply_rows = 32; h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + 32 * (size_t)h->ld) * 8; }
+    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem));
+    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem));
+    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem));
+    h->ql_smem = (size_t)2 * ff * 32 * 8;
+    CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->ql_smem));
+  }
+  // spill area: sized for the hungriest kernel (tail: Hq + up to 2 complex matrices)
+  h->scratch_ctas = std::max(std::max(h->front_grid, h->tri_grid), h->tail_grid);
+  h->scratch_stride = 2 * m2 + 2 * (2 * (size_t)ff * h->ld) + 16;
+  CUDA_TRY(dmalloc(&h->scratch, (size_t)h->scratch_ctas * h->scratch_stride));
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  *out = h;
+  return 0;
+}
+
+extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->cfg.device);
+  cudaFree(h->d_tw); cudaFree(h->d_Dk);
+  cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
+  cudaFree(h->rot_cs); cudaFree(h->rot_col); cudaFree(h->nrot); cudaFree(h->wstatus); cudaFree(h->scratch);
+  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+  return 0;
+}
+
+static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
+                        double* eff, double* de_r3, double* de_t3, int32_t* status, cudaStream_t st) {
+  KParams P;
+  memset(&P, 0, sizeof(P));
+  P.n_cells = h->cfg.n_cells; P.N = h->cfg.order; P.ff = h->ff; P.ld = h->ld; P.B = Bc;
+  P.n_inc = h->cfg.n_inc; P.n_exit = h->cfg.n_exit; P.eps_g = h->cfg.n_groove * h->cfg.n_groove;
+  P.tw = h->d_tw; P.Dk = h->d_Dk; P.patterns = patterns; P.params = params; P.pstride = pstride;
+  P.Cbuf = h->Cbuf; P.Lbuf = h->Lbuf; P.Wbuf = h->Wbuf; P.tri = h->tri; P.lam = h->lam;
+  P.rot_cs = h->rot_cs; P.rot_col = h->rot_col; P.nrot = h->nrot; P.maxrot = h->maxrot; P.wstatus = h->wstatus;
+  P.scratch = h->scratch; P.scratch_stride = h->scratch_stride;
+  P.eff = eff; P.de_r3 = de_r3; P.de_t3 = de_t3; P.status = status;
+
+  P.smem_mats = h->front_mats;
+  k_front<FRONT_NT><<<std::min(Bc, h->front_grid), FRONT_NT, h->front_smem, st>>>(P);
+  P.smem_mats = h->tri_mats;
+  k_tridiag<TRI_NT><<<std::min(Bc, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P);
+  k_ql<<<(Bc + 31) / 32, 32, h->ql_smem, st>>>(P);
+  {
+    dim3 g(Bc, (h->ff + h->apply_rows - 1) / h->apply_rows);
+    if (h->apply_rows == 96) k_apply<96><<<g, 96, h->apply_smem, st>>>(P);
+    else if (h->apply_rows == 64) k_apply<64><<<g, 64, h->apply_smem, st>>>(P);
+    else k_apply<32><<<g, 32, h->apply_smem, st>>>(P);
+  }
+  P.smem_mats = h->tail_mats;
+  const int tg = std::min(Bc, h->tail_grid);
+  if (h->ff <= 96) k_tail<TAIL_NT, 3><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
+  else if (h->ff <= 128) k_tail<TAIL_NT, 4><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
+  else k_tail<TAIL_NT, 8><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
+  h->launches += 5;
+  h->last_chunk = Bc;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                              int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status, void* stream) {
+  if (!h || !patterns || !params || !eff) return fail(-1, "null argument");
+  if (B < 0) return fail(-2, "negative batch");
+  if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
+  if (B == 0) return 0;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t mb = h->cfg.max_batch;
+  for (int64_t off = 0; off < B; off += mb) {
+    const int Bc = (int)std::min<int64_t>(mb, B - off);
+    int rc = launch_chunk(h, patterns + off * h->cfg.n_cells, params + off * param_stride, param_stride, Bc,
+                          eff + off, de_r3 ? de_r3 + 3 * off : nullptr, de_t3 ? de_t3 + 3 * off : nullptr,
+                          status ? status + off : nullptr, st);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+extern "C" int pirl_rcwa_eval_host(pirl_handle* h, const int8_t* patterns, const double* params,
+                                   int32_t param_stride, int64_t B, double* eff, double* de_r3, double* de_t3,
+                                   int32_t* status) {
+  if (!h || !patterns || !params || !eff) return fail(-1, "null argument");
+  if (B < 0) return fail(-2, "negative batch");
+  if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
+  if (B == 0) return 0;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  if (B > h->hd_cap) {
+    cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
+    h->hd_patterns = nullptr; h->hd_params = nullptr; h->hd_out = nullptr; h->hd_status = nullptr; h->hd_cap = 0;
+    CUDA_TRY(dmalloc(&h->hd_patterns, (size_t)B * h->cfg.n_cells));
+    CUDA_TRY(dmalloc(&h->hd_params, (size_t)B * 4));
+    CUDA_TRY(dmalloc(&h->hd_out, (size_t)B * 7));
+    CUDA_TRY(dmalloc(&h->hd_status, (size_t)B));
+    h->hd_cap = B;
+  }
+  cudaStream_t st = h->own_stream;
+  const size_t np = param_stride ? (size_t)B * 4 : 4;
+  CUDA_TRY(cudaMemcpyAsync(h->hd_patterns, patterns, (size_t)B * h->cfg.n_cells, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(h->hd_params, params, np * sizeof(double), cudaMemcpyHostToDevice, st));
+  double* d_eff = h->hd_out;
+  double* d_r3 = h->hd_out + B;
+  double* d_t3 = h->hd_out + 4 * B;
+  int rc = pirl_rcwa_eval(h, h->hd_patterns, h->hd_params, param_stride, B, d_eff, de_r3 ? d_r3 : nullptr,
+                          de_t3 ? d_t3 : nullptr, h->hd_status, st);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(eff, d_eff, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (de_r3) CUDA_TRY(cudaMemcpyAsync(de_r3, d_r3, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (de_t3) CUDA_TRY(cudaMemcpyAsync(de_t3, d_t3, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (status) CUDA_TRY(cudaMemcpyAsync(status, h->hd_status, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int pirl_env_flip(int8_t* patterns, const int64_t* actions, int64_t B, int32_t n_cells, void* stream) {
+  if (!patterns || !actions) return fail(-1, "null argument");
+  if (B <= 0) return 0;
+  k_env_flip<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(patterns, actions, B, n_cells);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int pirl_env_reward(const double* eff_new, double* eff_prev, double* reward, double* best_eff,
+                               int8_t* best_patterns, const int8_t* patterns, int64_t B, int32_t n_cells,
+                               void* stream) {
+  if (!eff_new || !eff_prev || !reward) return fail(-1, "null argument");
+  if (best_eff && best_patterns && !patterns) return fail(-2, "patterns required for best tracking");
+  if (B <= 0) return 0;
+  k_env_reward<<<(unsigned)B, 64, 0, (cudaStream_t)stream>>>(eff_new, eff_prev, reward, best_eff, best_patterns,
+                                                             patterns, B, n_cells);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int64_t pirl_rcwa_launch_count(pirl_handle* h) { return h ? h->launches : 0; }
+
+extern "C" int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, int64_t max_elems) {
+  if (!h || !dst) return fail(-1, "null argument");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  const size_t B = h->last_chunk, ff = h->ff;
+  const double* src = nullptr;
+  size_t n = 0;
+  switch (what) {
+    case 0: src = h->Cbuf; n = B * ff * ff; break;
+    case 1: src = h->tri; n = B * 2 * ff; break;
+    case 2: src = h->lam; n = B * ff; break;
+    case 3: src = h->Wbuf; n = B * ff * ff; break;
+    case 4: {
+      std::vector<int> tmp(B);
+      CUDA_TRY(cudaMemcpy(tmp.data(), h->nrot, B * sizeof(int), cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < B && (int64_t)i < max_elems; ++i) dst[i] = (double)tmp[i];
+      return 0;
+    }
+    default: return fail(-2, "unknown debug item");
+  }
+  if ((int64_t)n > max_elems) n = (size_t)max_elems;
+  CUDA_TRY(cudaMemcpy(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
