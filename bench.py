@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""bench.py -- deflector RCWA evaluations / second on B200 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W      (N > 1)
+
+A "step" = one pass of the hot path (pattern -> convolution matrices -> eigenmodes -> layer solve -> efficiency) over one
+batch of synthetic +-1 patterns: BASELINE.json configs[1] -- 4096 random 256-pixel patterns, 1100 nm / 60 deg,
+Fourier order 40, float64 -- PER GPU (weak scaling: structures shard across ranks, no data-path collective).
+
+  value          whole-job evaluations/s, inputs resident in HBM, device time by CUDA events, max over ranks
+  e2e            same metric through the host-buffer C-ABI entry (pirl_rcwa_eval_host): pinned host patterns -> H2D ->
+                 kernels -> D2H efficiencies, host wall clock with a device sync on both sides
+  roofline       dominant kernel: algorithmic FP64 flops of its stage / its CUDA-event duration, against the FP64 peak
+                 measured in this same run (cuBLAS DGEMM; MEASURED_PEAKS.json carries no FP64 figure)
+  cpu_baseline   oracle port (NumPy/LAPACK restatement of the reference formulation) on all host cores, bounded sample
+  --impl reference   the same CPU implementation as the timed arm (the reference is pure Python + NumPy; oracle/ is
+                 its restatement, pinned to the unmodified reference on the committed fixtures)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "deflector_rcwa_evals_per_sec"
+UNIT = "evals/s"
+WORKLOAD = "configs[1]: 4096 random 256-pixel patterns per GPU, 1100 nm / 60 deg, TM, order 40, float64 (complex128-equivalent)"
+
+
+def f_alg(ff: int) -> float:
+    """Algorithmic real FP64 flops per evaluation: (220/3) ff^3."""
+    return 220.0 / 3.0 * ff ** 3
+
+
+# stage shares of F_alg (in units of ff^3), SURVEY.md section 8d decomposition mapped onto the kernels
+STAGE_FLOPS_FF3 = {
+    "k_front": 4.0 + 4.0 / 3.0 + 4.0,          # inverse of E, factorisation of A, reduction to standard form
+    "k_tridiag": 16.0 / 3.0 + 16.0 / 3.0 + 4.0,  # Householder tridiagonalisation, accumulation of Q, back-substitution
+    "k_ql": 0.0,                               # O(ff^2) scalar recurrences
+    "k_apply": 12.0,                           # rotations applied to the ff x ff basis (steqr with vectors)
+    "k_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
+    "k_solve": 220.0 / 3.0,                    # fused whole-path kernel
+}
+
+
+def make_patterns(batch, n_cells, seed):
+    import numpy as np
+    return (np.random.default_rng(seed).integers(0, 2, (batch, n_cells)) * 2 - 1).astype(np.int8)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU every 100 ms while the timed region runs (NVML, else nvidia-smi)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag = index, threading.Event()
+        self.sm, self.reasons, self.sm_max, self.power = [], set(), None, []
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:  # noqa: BLE001
+            self.nv = None
+
+    _BITS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+             0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+             0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def _sample(self):
+        if self.nv is not None:
+            nv = self.nv
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+            try:
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception:  # noqa: BLE001
+                pass
+            try:
+                bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:  # noqa: BLE001
+                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for b, name in self._BITS.items():
+                if bits & b and name != "gpu_idle":
+                    self.reasons.add(name)
+        else:
+            import subprocess
+            out = subprocess.run(["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm,"
+                                  "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                                  "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
+                                  "--format=csv,noheader,nounits"], capture_output=True, text=True).stdout.strip()
+            f = [x.strip() for x in out.split(",")]
+            if len(f) >= 6:
+                self.sm.append(float(f[0])); self.sm_max = float(f[1])
+                for v, name in zip(f[2:6], ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(name)
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                self._sample()
+            except Exception:  # noqa: BLE001
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        import statistics
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "power_w_max": max(self.power) if self.power else None}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def cpu_baseline(patterns, order, wavelength, angle, thickness, budget_s=10.0):
+    """Oracle port on all host cores, bounded sample of the same workload (about ``budget_s`` of wall time)."""
+    import numpy as np
+    from oracle import cpu_pool
+    cores = cpu_pool.host_cores()
+    t1 = cpu_pool.single_eval_seconds(patterns[0], wavelength, angle, order, thickness)
+    per_core = int(min(512, max(4, budget_s / max(t1, 1e-4))))
+    count = cores * per_core
+    reps = -(-count // len(patterns))
+    sample = np.concatenate([patterns] * reps)[:count]
+    pool = cpu_pool.OraclePool(cores)
+    try:
+        pool.run(sample[: cores * 2], wavelength, angle, order, thickness)          # warm the workers
+        eff, dt = pool.run(sample, wavelength, angle, order, thickness)
+    finally:
+        pool.close()
+    return {"value": count / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{count} patterns of the workload ({per_core} per core, {dt:.1f} s wall), oracle/rcwa_oracle.py, "
+                      f"one process per core with 1 BLAS thread; single-core latency {t1 * 1e3:.1f} ms/eval",
+            "single_core_evals_per_s": 1.0 / t1}, eff, sample
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU formulation (oracle port; the reference is Python/NumPy and cannot
+    travel to the GPU box) on all host cores.  One step = a bounded sample of the configs[1] batch."""
+    import numpy as np
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import cpu_pool
+    cores = cpu_pool.host_cores()
+    pats = make_patterns(args.batch, args.n_cells, 1234)
+    per_step = int(min(args.batch, max(256, 64 * cores)))
+    sample = pats[:per_step]
+    pool = cpu_pool.OraclePool(cores)
+    try:
+        for _ in range(args.warmup):
+            pool.run(sample, args.wavelength, args.angle, args.order, args.thickness)
+        total = 0.0
+        for _ in range(args.steps):
+            _, dt = pool.run(sample, args.wavelength, args.angle, args.order, args.thickness)
+            total += dt
+    finally:
+        pool.close()
+    value = per_step * args.steps / total
+    desc = (f"{per_step} of the {args.batch} patterns per step, oracle/rcwa_oracle.py (NumPy/LAPACK restatement of the "
+            f"reference formulation), one process per core, 1 BLAS thread each")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "n_cells": args.n_cells, "order": args.order, "batch_per_step": per_step},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def measure_fp64_peak(torch, n=8192, reps=6):
+    """cuBLAS DGEMM n^3, best of ``reps`` (burst figure): the FP64 roofline denominator, TFLOP/s."""
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    b = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    c = torch.empty_like(a)
+    torch.matmul(a, b, out=c)
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, b, out=c); e1.record(); e1.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b, c
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def run_b200(args):
+    import numpy as np
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("for --gpus N > 1 launch with torch.distributed.run --nproc-per-node N")
+
+    ff = 2 * args.order + 1
+    pats_np = make_patterns(args.batch, args.n_cells, 1234 + rank)
+
+    # CPU baseline first (rank 0, N=1 only), before CUDA is initialised in this process
+    cpu = None
+    cpu_check = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu, cpu_eff, cpu_sample = cpu_baseline(pats_np, args.order, args.wavelength, args.angle, args.thickness,
+                                                args.cpu_budget)
+        cpu_check = (cpu_eff, cpu_sample)
+
+    import torch
+    import torch.distributed as dist
+    from physics_informed_reinforcement_learning_b200 import RCWABatch, max_over_ranks
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    be = RCWABatch(args.n_cells, args.order, max_batch=args.batch, device=local_rank)
+    d_pats = torch.from_numpy(pats_np).to(dev)
+    params_rows, _ = be._params(1, args.wavelength, args.angle, args.thickness, None)
+    d_params = torch.from_numpy(params_rows).to(dev)
+    flush = torch.empty(384 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    fp64_peak = measure_fp64_peak(torch) if rank == 0 else None
+
+    # ---- device-resident arm -------------------------------------------------------------------------------------
+    eff = None
+    for _ in range(max(args.warmup, 3)):
+        eff = be.evaluate(d_pats, params=d_params)
+    torch.cuda.synchronize()
+    eff_first = eff.clone()
+
+    sampler = ClockSampler(local_rank)
+    be.set_stage_timing(True)
+    be.stage_times()
+    l0 = be.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    sampler.start()
+    for a, b in ev:
+        flush.fill_(1)                       # evict L2 between timed iterations (untimed)
+        a.record()
+        eff = be.evaluate(d_pats, params=d_params)
+        b.record()
+    barrier()
+    launches = be.launch_count() - l0
+    stage = be.stage_times()
+    be.set_stage_timing(False)
+    dev_s = sum(a.elapsed_time(b) for a, b in ev) * 1e-3
+    job_s = max_over_ranks(dev_s, device=dev)
+    assert torch.equal(eff, eff_first), "non-deterministic result"
+
+    # ---- end-to-end arm: host buffers through pirl_rcwa_eval_host ----------------------------------------------
+    h_pats = torch.from_numpy(pats_np).pin_memory()
+    h_eff = torch.empty(args.batch, dtype=torch.float64).pin_memory()
+    h_st = torch.empty(args.batch, dtype=torch.int32).pin_memory()
+    hp, he, hs = h_pats.numpy(), h_eff.numpy(), h_st.numpy()
+    for _ in range(2):
+        be.evaluate_host(hp, args.wavelength, args.angle, args.thickness, out=he, status_out=hs)
+    barrier()
+    e2e_s = 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        be.evaluate_host(hp, args.wavelength, args.angle, args.thickness, out=he, status_out=hs)   # synchronous
+        e2e_s += time.perf_counter() - t0
+    barrier()
+    sampler.stop_flag.set()
+    sampler.join()
+    e2e_job_s = max_over_ranks(e2e_s, device=dev)
+    assert int(np.abs(hs).sum()) == 0, "solver status flags set"
+    assert np.array_equal(he, eff.cpu().numpy()), "host entry and device entry disagree"
+
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- parity of the timed workload against the CPU baseline's own outputs -----------------------------------
+    parity = None
+    if cpu_check is not None:
+        cpu_eff, cpu_sample = cpu_check
+        n = min(len(cpu_eff), args.batch)
+        parity = float(np.abs(cpu_eff[:n] - he[:n]).max())
+        assert parity <= 1e-6, f"GPU efficiencies differ from the CPU oracle by {parity}"
+
+    total_evals = args.batch * world * args.steps
+    value = total_evals / job_s
+    # dominant kernel
+    name, (ms, cnt) = max(stage.items(), key=lambda kv: kv[1][0])
+    per_launch_s = ms * 1e-3 / max(cnt, 1)
+    structs_per_launch = args.batch * args.steps / max(cnt, 1)
+    flops_per_launch = STAGE_FLOPS_FF3.get(name, 0.0) * ff ** 3 * structs_per_launch
+    achieved = flops_per_launch / per_launch_s / 1e12
+    stage_total = sum(v[0] for v in stage.values())
+    roofline = {"bound": "tensor", "kernel": name, "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+                "frac": achieved / fp64_peak, "traffic": None,
+                "peak_source": "FP64: cuBLAS DGEMM 8192^3 best of 6 measured in this run (MEASURED_PEAKS.json has no FP64 row)",
+                "flops_per_launch": flops_per_launch, "ms_per_launch": per_launch_s * 1e3,
+                "share_of_step": ms / stage_total if stage_total else None,
+                "path": {"flops_per_eval": f_alg(ff), "achieved": value / world * f_alg(ff) / 1e12,
+                         "frac": value / world * f_alg(ff) / 1e12 / fp64_peak},
+                "stages_ms_per_step": {k: v[0] / args.steps for k, v in stage.items()}}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": job_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "n_cells": args.n_cells, "order": args.order, "batch_per_gpu": args.batch,
+                       "global_batch": args.batch * world, "wavelength_nm": args.wavelength, "angle_deg": args.angle,
+                       "thickness_nm": args.thickness, "parallelism": f"structures sharded over {world} GPU(s)",
+                       "l2": "384 MiB flush between timed iterations; workspaces (3 x 215 MB) exceed L2"},
+            "e2e": {"value": total_evals / e2e_job_s, "unit": UNIT,
+                    "h2d_bytes_per_step": int(hp.nbytes + 32), "d2h_bytes_per_step": int(he.nbytes + hs.nbytes),
+                    "ms_per_step": e2e_job_s / args.steps * 1e3},
+            "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roofline,
+            "parity_max_abs_err_vs_cpu": parity}
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=4096, help="structures per GPU per step")
+    ap.add_argument("--n-cells", type=int, default=256)
+    ap.add_argument("--order", type=int, default=40)
+    ap.add_argument("--wavelength", type=float, default=1100.0)
+    ap.add_argument("--angle", type=float, default=60.0)
+    ap.add_argument("--thickness", type=float, default=325.0)
+    ap.add_argument("--cpu-budget", type=float, default=10.0, help="seconds of wall time for the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -87,6 +87,15 @@ int pirl_env_reward(const double* eff_new, double* eff_prev, double* reward, dou
 /* Number of kernels this library launched since the handle was created (bench.py's gpu_launches). */
 int64_t pirl_rcwa_launch_count(pirl_handle* h);
 
+/* Per-kernel device timing (bench.py's roofline): when enabled, every kernel launched by pirl_rcwa_eval is
+ * bracketed by CUDA events on the caller's stream.  pirl_rcwa_stage_times synchronises those events, ADDS the
+ * elapsed milliseconds per stage into ms[0..num_stages) and the launch counts into launches[0..num_stages)
+ * (either may be NULL), and clears the internal record. */
+int pirl_rcwa_num_stages(void);
+const char* pirl_rcwa_stage_name(int32_t stage);
+int pirl_rcwa_set_stage_timing(pirl_handle* h, int32_t enable);
+int pirl_rcwa_stage_times(pirl_handle* h, double* ms, int64_t* launches);
+
 /* Test hook: copy a stage intermediate of the LAST chunk evaluated to a host buffer.
  * what: 0 = reduced standard-form matrix C [B][ff][ff], 1 = tridiagonal d,e [B][2][ff],
  *       2 = eigenvalues [B][ff], 3 = modes W (A-orthonormal, real basis) [B][ff][ff],

@@ -10,7 +10,7 @@ Public surface:
 from .solver import RCWABatch, JLABCode, shared_backend  # noqa: F401
 from .envs import MeentIndex, VectorDeflectorEnv, make, random_bunch_init  # noqa: F401
 from .materials import find_nk_index, n_silicon_real  # noqa: F401
-from .dist import shard_range, gather_efficiencies  # noqa: F401
+from .dist import shard_range, gather_efficiencies, max_over_ranks  # noqa: F401
 
 __all__ = ["RCWABatch", "JLABCode", "shared_backend", "MeentIndex", "VectorDeflectorEnv", "make",
            "random_bunch_init", "find_nk_index", "n_silicon_real", "shard_range", "gather_efficiencies"]

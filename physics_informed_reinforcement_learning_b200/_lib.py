@@ -9,6 +9,7 @@ from .build import LIB_PATH
 SYMBOLS = [
     "pirl_abi_version", "pirl_last_error", "pirl_rcwa_create", "pirl_rcwa_destroy", "pirl_rcwa_eval",
     "pirl_rcwa_eval_host", "pirl_env_flip", "pirl_env_reward", "pirl_rcwa_launch_count", "pirl_rcwa_debug_fetch",
+    "pirl_rcwa_num_stages", "pirl_rcwa_stage_name", "pirl_rcwa_set_stage_timing", "pirl_rcwa_stage_times",
 ]
 
 
@@ -45,8 +46,13 @@ def load():
     lib.pirl_rcwa_launch_count.argtypes = [vp]
     lib.pirl_rcwa_launch_count.restype = C.c_int64
     lib.pirl_rcwa_debug_fetch.argtypes = [vp, i32, dp, i64]
+    lib.pirl_rcwa_num_stages.restype = C.c_int
+    lib.pirl_rcwa_stage_name.argtypes = [i32]
+    lib.pirl_rcwa_stage_name.restype = C.c_char_p
+    lib.pirl_rcwa_set_stage_timing.argtypes = [vp, i32]
+    lib.pirl_rcwa_stage_times.argtypes = [vp, dp, dp]
     for name in ("pirl_rcwa_create", "pirl_rcwa_destroy", "pirl_rcwa_eval", "pirl_rcwa_eval_host", "pirl_env_flip",
-                 "pirl_env_reward", "pirl_rcwa_debug_fetch"):
+                 "pirl_env_reward", "pirl_rcwa_debug_fetch", "pirl_rcwa_set_stage_timing", "pirl_rcwa_stage_times"):
         getattr(lib, name).restype = C.c_int
     _lib = lib
     return lib

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 #include <algorithm>
 
@@ -51,6 +52,29 @@ struct pirl_handle {
   int8_t* hd_patterns = nullptr; double* hd_params = nullptr; double* hd_out = nullptr; int32_t* hd_status = nullptr;
   int64_t hd_cap = 0;
   cudaStream_t own_stream = nullptr;
+  // per-kernel timing (pirl_rcwa_set_stage_timing)
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_free;
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
+};
+
+static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail"};
+static constexpr int kNumStages = 5;
+
+static cudaEvent_t take_event(pirl_handle* h) {
+  if (!h->ev_free.empty()) { cudaEvent_t e = h->ev_free.back(); h->ev_free.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+struct StageTimer {   // brackets one kernel launch with events when timing is on
+  pirl_handle* h; int stage; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
+  StageTimer(pirl_handle* h_, int stage_, cudaStream_t st_) : h(h_), stage(stage_), st(st_) {
+    if (h->timing) { a = take_event(h); b = take_event(h); cudaEventRecord(a, st); }
+  }
+  ~StageTimer() {
+    if (h->timing) { cudaEventRecord(b, st); h->ev_pending.push_back({stage, {a, b}}); }
+  }
 };
 
 extern "C" int pirl_abi_version(void) { return PIRL_ABI_VERSION; }
@@ -140,7 +164,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->front_smem = vec + h->front_mats * rmat;
     int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / FRONT_NT, budget / std::max<size_t>(h->front_smem + 1024, 1)));
     h->front_grid = h->sm_count * per_sm;
-    CUDA_TRY(cudaFuncSetAttribute(k_front<FRONT_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->front_smem));
+    CUDA_TRY(cudaFuncSetAttribute(k_front<FRONT_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
   }
   {
     size_t vec = (size_t)tridiag_vec_doubles(ff) * 8;
@@ -148,7 +172,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->tri_smem = vec + h->tri_mats * rmat;
     int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / TRI_NT, budget / std::max<size_t>(h->tri_smem + 1024, 1)));
     h->tri_grid = h->sm_count * per_sm;
-    CUDA_TRY(cudaFuncSetAttribute(k_tridiag<TRI_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tri_smem));
+    CUDA_TRY(cudaFuncSetAttribute(k_tridiag<TRI_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
   }
   {
     size_t vec = (size_t)tail_vec_doubles(ff) * 8;
@@ -156,19 +180,19 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->tail_smem = vec + h->tail_mats * cmat;
     int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / TAIL_NT, budget / std::max<size_t>(h->tail_smem + 1024, 1)));
     h->tail_grid = h->sm_count * per_sm;
-    if (ff <= 96) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem));
-    else if (ff <= 128) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem));
-    else CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem));
+    if (ff <= 96) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    else if (ff <= 128) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    else CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
   }
   {
     h->apply_rows = (ff <= 96) ? 96 : 64;
     h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + (size_t)h->apply_rows * h->ld) * 8;
     if (h->apply_smem > budget) { h->apply_rows = 32; h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + 32 * (size_t)h->ld) * 8; }
-    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem));
-    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem));
-    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem));
+    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
     h->ql_smem = (size_t)2 * ff * 32 * 8;
-    CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->ql_smem));
+    CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
   }
   // spill area: sized for the hungriest kernel (tail: Hq + up to 2 complex matrices)
   h->scratch_ctas = std::max(std::max(h->front_grid, h->tri_grid), h->tail_grid);
@@ -187,6 +211,8 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaFree(h->rot_cs); cudaFree(h->rot_col); cudaFree(h->nrot); cudaFree(h->wstatus); cudaFree(h->scratch);
   cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  for (auto& p : h->ev_pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
+  for (auto e : h->ev_free) cudaEventDestroy(e);
   delete h;
   return 0;
 }
@@ -204,11 +230,12 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   P.eff = eff; P.de_r3 = de_r3; P.de_t3 = de_t3; P.status = status;
 
   P.smem_mats = h->front_mats;
-  k_front<FRONT_NT><<<std::min(Bc, h->front_grid), FRONT_NT, h->front_smem, st>>>(P);
+  { StageTimer t(h, 0, st); k_front<FRONT_NT><<<std::min(Bc, h->front_grid), FRONT_NT, h->front_smem, st>>>(P); }
   P.smem_mats = h->tri_mats;
-  k_tridiag<TRI_NT><<<std::min(Bc, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P);
-  k_ql<<<(Bc + 31) / 32, 32, h->ql_smem, st>>>(P);
+  { StageTimer t(h, 1, st); k_tridiag<TRI_NT><<<std::min(Bc, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P); }
+  { StageTimer t(h, 2, st); k_ql<<<(Bc + 31) / 32, 32, h->ql_smem, st>>>(P); }
   {
+    StageTimer t(h, 3, st);
     dim3 g(Bc, (h->ff + h->apply_rows - 1) / h->apply_rows);
     if (h->apply_rows == 96) k_apply<96><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 64) k_apply<64><<<g, 64, h->apply_smem, st>>>(P);
@@ -216,12 +243,36 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   }
   P.smem_mats = h->tail_mats;
   const int tg = std::min(Bc, h->tail_grid);
+  StageTimer t(h, 4, st);
   if (h->ff <= 96) k_tail<TAIL_NT, 3><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
   else if (h->ff <= 128) k_tail<TAIL_NT, 4><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
   else k_tail<TAIL_NT, 8><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
   h->launches += 5;
   h->last_chunk = Bc;
   CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int pirl_rcwa_num_stages(void) { return kNumStages; }
+extern "C" const char* pirl_rcwa_stage_name(int32_t s) { return (s >= 0 && s < kNumStages) ? kStageNames[s] : ""; }
+extern "C" int pirl_rcwa_set_stage_timing(pirl_handle* h, int32_t enable) {
+  if (!h) return fail(-1, "null argument");
+  h->timing = enable != 0;
+  return 0;
+}
+extern "C" int pirl_rcwa_stage_times(pirl_handle* h, double* ms, int64_t* launches) {
+  if (!h) return fail(-1, "null argument");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  for (auto& p : h->ev_pending) {
+    CUDA_TRY(cudaEventSynchronize(p.second.second));
+    float t = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&t, p.second.first, p.second.second));
+    if (ms) ms[p.first] += (double)t;
+    if (launches) launches[p.first] += 1;
+    h->ev_free.push_back(p.second.first);
+    h->ev_free.push_back(p.second.second);
+  }
+  h->ev_pending.clear();
   return 0;
 }
 

@@ -115,16 +115,21 @@ class RCWABatch:
         return eff
 
     def evaluate_host(self, patterns, wavelength=1100.0, angle=60.0, thickness=325.0, n_ridge=None,
-                      return_orders=False):
+                      return_orders=False, out=None, status_out=None):
         """patterns: numpy [B, n_cells] (any real dtype, >0 = ridge).  Host buffers in, host buffers out;
-        the H2D/D2H copies happen inside the library call (``pirl_rcwa_eval_host``)."""
-        pat = np.ascontiguousarray(np.where(np.asarray(patterns) > 0, 1, -1).astype(np.int8))
+        the H2D/D2H copies happen inside the library call (``pirl_rcwa_eval_host``).  ``out`` / ``status_out``:
+        optional preallocated float64 [B] / int32 [B] result buffers (e.g. pinned memory)."""
+        pat = np.asarray(patterns)
         if pat.ndim != 2 or pat.shape[1] != self.n_cells:
             raise ValueError(f"patterns must be [B, {self.n_cells}]")
+        if pat.dtype != np.int8 or not pat.flags.c_contiguous:
+            pat = np.ascontiguousarray(np.where(pat > 0, 1, -1).astype(np.int8))
         B = pat.shape[0]
         rows, stride = self._params(B, wavelength, angle, thickness, n_ridge)
-        eff = np.empty(B, dtype=np.float64)
-        st = np.empty(B, dtype=np.int32)
+        eff = np.empty(B, dtype=np.float64) if out is None else out
+        st = np.empty(B, dtype=np.int32) if status_out is None else status_out
+        if eff.dtype != np.float64 or eff.shape != (B,) or st.dtype != np.int32 or st.shape != (B,):
+            raise ValueError("out must be float64 [B] and status_out int32 [B]")
         r3 = np.empty((B, 3), dtype=np.float64) if return_orders else None
         t3 = np.empty((B, 3), dtype=np.float64) if return_orders else None
         _lib.check(self.lib.pirl_rcwa_eval_host(
@@ -136,6 +141,18 @@ class RCWABatch:
 
     def launch_count(self) -> int:
         return int(self.lib.pirl_rcwa_launch_count(self._h))
+
+    def set_stage_timing(self, enable: bool):
+        """Bracket every kernel of ``evaluate`` with CUDA events on the launching stream (bench.py's roofline)."""
+        _lib.check(self.lib.pirl_rcwa_set_stage_timing(self._h, 1 if enable else 0))
+
+    def stage_times(self):
+        """{kernel name: (total ms, launches)} since the last call; synchronises the recorded events."""
+        n = self.lib.pirl_rcwa_num_stages()
+        ms = np.zeros(n, dtype=np.float64)
+        cnt = np.zeros(n, dtype=np.int64)
+        _lib.check(self.lib.pirl_rcwa_stage_times(self._h, ms.ctypes.data, cnt.ctypes.data))
+        return {self.lib.pirl_rcwa_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}
 
     def debug_fetch(self, what: str, B: int):
         ff = self.ff

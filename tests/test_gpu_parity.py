@@ -1,0 +1,296 @@
+"""GPU (B200): the CUDA path, called through the C-ABI library, against
+
+  * the committed fixtures produced by the UNMODIFIED reference solver (tests/golden/*.npz, oracle/make_golden.py),
+  * the CPU oracle (oracle/rcwa_oracle.py) on freshly seeded inputs at sizes it finishes in seconds,
+  * size-independent properties at BASELINE.json's full batch sizes (translation / mirror symmetry, chunking
+    idempotence, determinism).
+
+Tolerance: |d efficiency| <= 1e-6 absolute (north_star, complex128 mode).  The observed error is ~1e-12; a second,
+tighter assertion (1e-9) guards against silent precision regressions.
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-6        # north_star: diffraction efficiencies within 1e-6 absolute in complex128
+TIGHT = 1e-9      # regression guard (float64 path; measured ~1e-12)
+
+
+@pytest.fixture(scope="module")
+def torch_mod():
+    import torch
+    assert torch.cuda.is_available()
+    torch.cuda.set_device(0)
+    return torch
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import physics_informed_reinforcement_learning_b200 as p
+    return p
+
+
+def _named(golden_dir):
+    g = np.load(os.path.join(golden_dir, "rcwa_golden.npz"))
+    names = sorted({k.split("/")[0] for k in g.files})
+    return g, names
+
+
+def test_named_golden_cases_through_c_abi_host_entry(golden_dir, pkg, torch_mod):
+    """Every named reference case (G1..G8, Reticolo known answer), through pirl_rcwa_eval_host."""
+    g, names = _named(golden_dir)
+    backends = {}
+    worst = 0.0
+    for n in names:
+        pat = g[n + "/pattern"]
+        order = int(g[n + "/order"])
+        key = (pat.size, order)
+        if key not in backends:
+            backends[key] = pkg.RCWABatch(pat.size, order, max_batch=8)
+        be = backends[key]
+        eff, r3, t3, st = be.evaluate_host(pat[None, :], float(g[n + "/wavelength"]), float(g[n + "/angle"]),
+                                           float(g[n + "/thickness"]), return_orders=True)
+        assert st[0] == 0, (n, st)
+        e = abs(eff[0] - float(g[n + "/ref_eff"]))
+        # reference cuts are [::-1] of de[N-1:N+2]
+        et = np.abs(t3[0][::-1] - g[n + "/ref_tran_cut"]).max()
+        er = np.abs(r3[0][::-1] - g[n + "/ref_refl_cut"]).max()
+        worst = max(worst, e, et, er)
+        assert e <= TOL and et <= TOL and er <= TOL, (n, e, et, er)
+    assert worst <= TIGHT, worst
+    for be in backends.values():
+        be.close()
+
+
+def test_reticolo_known_answer(golden_dir, pkg):
+    g, _ = _named(golden_dir)
+    n = "KA_reticolo_800nm_70deg"
+    be = pkg.RCWABatch(256, 40, max_batch=4)
+    eff = be.evaluate_host(np.stack([g[n + "/pattern"], g[n + "/pattern"][::-1]]), 800.0, 70.0, 325.0)
+    assert abs(eff[0] - float(g[n + "/reticolo_efficiency"])) < 5e-8      # float32 rounding of the recorded value
+    assert abs(eff[1] - 0.027283368919125597) < TIGHT                     # orientation pin
+    be.close()
+
+
+def test_batch_fixture_device_entry(golden_dir, pkg, torch_mod):
+    """256 mixed random / blocky patterns at the headline geometry, device-resident entry (pirl_rcwa_eval)."""
+    torch = torch_mod
+    b = np.load(os.path.join(golden_dir, "rcwa_batch.npz"))
+    be = pkg.RCWABatch(256, 40, max_batch=100)        # 256 = 100 + 100 + 56: exercises ragged chunking
+    pats = torch.from_numpy(b["patterns"]).cuda()
+    eff, r3, t3, st = be.evaluate(pats, 1100.0, 60.0, 325.0, return_orders=True)
+    torch.cuda.synchronize()
+    assert int(st.abs().sum()) == 0
+    eff, r3, t3 = eff.cpu().numpy(), r3.cpu().numpy(), t3.cpu().numpy()
+    assert np.abs(eff - b["ref_eff"]).max() <= TIGHT
+    assert np.abs(t3[:, ::-1] - b["ref_tran_cut"]).max() <= TIGHT
+    assert np.abs(r3[:, ::-1] - b["ref_refl_cut"]).max() <= TIGHT
+    assert b["ref_eff"].max() > 0.5
+    be.close()
+
+
+def test_sweep_fixture_per_structure_parameters(golden_dir, pkg, torch_mod):
+    """(wavelength, angle) grid at N=60 evaluated as ONE batch with per-structure parameter rows (config C4)."""
+    s = np.load(os.path.join(golden_dir, "rcwa_sweep.npz"))
+    grid = s["grid"]
+    pats = s["patterns"][grid[:, 2].astype(int)]
+    be = pkg.RCWABatch(256, int(s["order"]), max_batch=64)
+    eff = be.evaluate_host(pats, grid[:, 0], grid[:, 1], float(s["thickness"]))
+    assert np.abs(eff - grid[:, 3]).max() <= TIGHT
+    be.close()
+
+
+@pytest.mark.parametrize("n_cells,order,count", [(256, 40, 48), (64, 8, 32), (256, 60, 12), (512, 100, 3), (100, 17, 8)])
+def test_against_oracle_on_seeded_inputs(pkg, n_cells, order, count):
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(1000 + n_cells + order)
+    pats = rng.choice([-1, 1], (count, n_cells)).astype(np.int8)
+    for i in range(1, count, 3):                          # blocky rows: efficiencies far from the noise floor
+        blk = (4, 10, 16)[i % 3] if n_cells % 16 else (8, 16, 32)[i % 3]
+        base = rng.choice([-1, 1], -(-n_cells // blk))
+        pats[i] = np.repeat(base, blk)[:n_cells]
+    wl, ang, thick = 1100.0, 60.0, 325.0
+    be = pkg.RCWABatch(n_cells, order, max_batch=16)
+    eff, r3, t3, st = be.evaluate_host(pats, wl, ang, thick, return_orders=True)
+    assert not st.any()
+    for i in range(count):
+        r = O.evaluate(pats[i].astype(np.float64), wl, ang, order, thick)
+        assert abs(eff[i] - r.eff) <= TIGHT, (i, eff[i], r.eff)
+        assert np.abs(t3[i] - r.de_ti[order - 1:order + 2]).max() <= TIGHT
+        assert np.abs(r3[i] - r.de_ri[order - 1:order + 2]).max() <= TIGHT
+    be.close()
+
+
+def test_other_wavelengths_angles_thickness_vs_oracle(pkg):
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(77)
+    pats = np.repeat(rng.choice([-1, 1], (6, 32)), 8, axis=1).astype(np.int8)
+    wls = np.array([900.0, 950.0, 1000.0, 1100.0, 1200.0, 800.0])
+    angs = np.array([50.0, 55.0, 65.0, 70.0, 75.0, 60.0])
+    ths = np.array([325.0, 300.0, 250.0, 400.0, 325.0, 500.0])
+    be = pkg.RCWABatch(256, 40, max_batch=8)
+    eff = be.evaluate_host(pats, wls, angs, ths)
+    ref = np.array([O.efficiency(p.astype(float), w, a, 40, t) for p, w, a, t in zip(pats, wls, angs, ths)])
+    assert np.abs(eff - ref).max() <= TIGHT
+    be.close()
+
+
+def test_trivial_and_edge_inputs(pkg, torch_mod):
+    torch = torch_mod
+    be = pkg.RCWABatch(256, 40, max_batch=8)
+    pats = np.ones((3, 256), dtype=np.int8)
+    pats[1] = -1
+    pats[2, ::2] = -1                                        # finest possible grating
+    eff, r3, t3, st = be.evaluate_host(pats, return_orders=True)
+    assert not st.any()
+    assert abs(eff[0]) < 1e-15 and abs(eff[1]) < 1e-15        # uniform slabs diffract nothing (G3)
+    assert abs(r3[0, 1] + t3[0, 1] - 1.0) < 1e-10             # ... and conserve energy in the zeroth order
+    # empty batch: allowed, returns empty
+    e0 = be.evaluate(torch.empty(0, 256, dtype=torch.int8, device="cuda"))
+    assert e0.numel() == 0
+    assert be.evaluate_host(np.ones((0, 256))).size == 0
+    # wrong shapes / dtypes are rejected on the host
+    with pytest.raises(ValueError):
+        be.evaluate_host(np.ones((2, 255)))
+    with pytest.raises(TypeError):
+        be.evaluate(torch.ones(2, 256, device="cuda"))
+    with pytest.raises(ValueError):
+        be.evaluate_host(np.ones((3, 256)), wavelength=[1000.0, 1100.0])
+    be.close()
+
+
+def test_full_batch_properties_4096(pkg, torch_mod):
+    """BASELINE config C2 size (4096 x 256, N=40): properties that need no oracle.
+
+    * a circular shift of the pattern only multiplies every Fourier coefficient by a phase -> efficiencies unchanged;
+    * mirroring x -> -x swaps the +1 and -1 orders;
+    * chunked evaluation == one-shot evaluation, bit for bit; repeated evaluation is deterministic;
+    * lossless structure: de_r, de_t in [0, 1], the three central orders never exceed total power."""
+    torch = torch_mod
+    rng = np.random.default_rng(1234)
+    pats = (rng.integers(0, 2, (4096, 256)) * 2 - 1).astype(np.int8)
+    pats[::4] = np.repeat(rng.choice([-1, 1], (1024, 16)), 16, axis=1)
+    be = pkg.RCWABatch(256, 40, max_batch=4096)
+    dp = torch.from_numpy(pats).cuda()
+    eff, r3, t3, st = be.evaluate(dp, return_orders=True)
+    eff2 = be.evaluate(dp)
+    shifts = torch.from_numpy(rng.integers(1, 256, 4096)).cuda()
+    idx = (torch.arange(256, device="cuda")[None, :] + shifts[:, None]) % 256
+    eff_shift = be.evaluate(torch.gather(dp, 1, idx))
+    effm, r3m, t3m, _ = be.evaluate(torch.flip(dp, dims=[1]).contiguous(), return_orders=True)
+    be_small = pkg.RCWABatch(256, 40, max_batch=1000)
+    eff_chunk = be_small.evaluate(dp)
+    torch.cuda.synchronize()
+    assert int(st.abs().sum()) == 0
+    assert torch.equal(eff, eff2)
+    assert torch.equal(eff, eff_chunk)
+    assert (eff - eff_shift).abs().max().item() <= 1e-9
+    assert (t3[:, 0] - t3m[:, 2]).abs().max().item() <= 1e-9 and (t3[:, 2] - t3m[:, 0]).abs().max().item() <= 1e-9
+    assert (r3[:, 0] - r3m[:, 2]).abs().max().item() <= 1e-9
+    tot = r3.sum(1) + t3.sum(1)
+    assert (tot <= 1.0 + 1e-9).all() and (r3 >= -1e-12).all() and (t3 >= -1e-12).all()
+    assert eff.max().item() > 0.3
+    be.close(); be_small.close()
+
+
+def test_full_batch_sample_vs_oracle_4096(pkg, torch_mod):
+    """The C2 workload itself (default_rng(1234) patterns): a strided sample of 64 of the 4096 against the oracle."""
+    from oracle import rcwa_oracle as O
+    torch = torch_mod
+    pats = (np.random.default_rng(1234).integers(0, 2, (4096, 256)) * 2 - 1).astype(np.int8)
+    be = pkg.RCWABatch(256, 40, max_batch=4096)
+    eff = be.evaluate(torch.from_numpy(pats).cuda()).cpu().numpy()
+    idx = np.arange(0, 4096, 64)
+    ref = np.array([O.efficiency(pats[i].astype(float)) for i in idx])
+    assert np.abs(eff[idx] - ref).max() <= TIGHT
+    be.close()
+
+
+def test_jlabcode_and_meentindex_drop_in(golden_dir, pkg):
+    """The reference-facing API: JLABCode(...).reproduce_acs_cell and MeentIndex.reset/step/get_efficiency."""
+    g, _ = _named(golden_dir)
+    n = "G7_block16_N40"
+    pat = g[n + "/pattern"]
+    wls = np.array([1100])
+    period = abs(wls / np.sin(60 / 180 * np.pi))
+    calc = pkg.JLABCode(grating_type=0, n_I=1.45, n_II=1., theta=0, phi=0., fourier_order=40, period=period, wls=wls,
+                        pol=1, patterns=None, ucell=pat[np.newaxis, np.newaxis, :], thickness=np.array([325]))
+    eff, refl_cut, tran_cut = calc.reproduce_acs_cell('p_si__real', 1)
+    assert abs(eff - float(g[n + "/ref_eff"])) <= TIGHT
+    assert np.abs(tran_cut - g[n + "/ref_tran_cut"]).max() <= TIGHT
+    assert np.abs(refl_cut - g[n + "/ref_refl_cut"]).max() <= TIGHT
+    with pytest.raises(ValueError):
+        pkg.JLABCode(grating_type=1, ucell=pat[None, None, :])
+    with pytest.raises(ValueError):
+        pkg.JLABCode(pol=2, ucell=pat[None, None, :])
+
+    env = pkg.make('MeentIndex-v0', wavelength=1100, desired_angle=60, thickness=325)
+    assert env.observation_space.shape == (256,) and env.action_space.n == 256
+    np.random.seed(42)
+    obs = env.reset()
+    assert list(np.nonzero(obs == -1)[0]) == [31, 85, 176, 253]                    # SURVEY G5 (bit-exact reset)
+    assert abs(env.eff - float(g["G5_bunch_seed42/ref_eff"])) <= TIGHT
+    e0 = env.eff
+    obs2, reward, done, info = env.step(100)
+    assert obs2[100] == -1 and done is False and info == {}
+    assert reward == env.eff - e0
+    obs3, r3, _, _ = env.step(256)                                                 # out of range: no-op
+    assert np.array_equal(obs3, obs2) and r3 == 0.0
+    # G8: flip delta on the block pattern
+    env.struct = pat.copy()
+    env.eff = env.get_efficiency(env.struct)
+    _, rew, _, _ = env.step(100)
+    ref_delta = float(g["G8_block16_flip100/ref_eff"]) - float(g[n + "/ref_eff"])
+    assert abs(rew - ref_delta) <= 2 * TIGHT
+
+
+def test_vector_env_matches_scalar_semantics_bit_exact(pkg, torch_mod):
+    """VectorDeflectorEnv vs the restated MeentIndex semantics (oracle/env_oracle.py) driven by the SAME efficiency
+    values: patterns, observations, dones bit-exact; rewards equal to the float64 difference of the two efficiencies."""
+    from oracle import env_oracle
+    torch = torch_mod
+    B, T = 6, 9
+    be = pkg.RCWABatch(256, 40, max_batch=64)
+    env = pkg.VectorDeflectorEnv(B, backend=be, max_episode_steps=4)
+    np.random.seed(7)
+    obs = env.reset()
+    np.random.seed(7)
+    scal = [env_oracle.ScalarEnv(lambda s: float(be.evaluate_host(s[None, :])[0]), max_episode_steps=4) for _ in range(B)]
+    sobs = np.stack([e.reset() for e in scal])
+    assert np.array_equal(obs.cpu().numpy(), sobs)
+    assert np.array_equal(env.eff.cpu().numpy(), np.array([e.eff for e in scal]))
+    rng = np.random.default_rng(5)
+    for t in range(T):
+        acts = rng.integers(-2, 260, B)
+        obs, rew, done, info = env.step(acts, auto_reset=False)
+        outs = [e.step(int(a)) for e, a in zip(scal, acts)]
+        assert np.array_equal(obs.cpu().numpy(), np.stack([o[0] for o in outs]))
+        assert np.array_equal(rew.cpu().numpy(), np.array([o[1] for o in outs]))      # bit-exact f64 subtraction
+        assert np.array_equal(done.cpu().numpy(), np.array([o[2] for o in outs]))
+        assert np.array_equal(env.best_eff.cpu().numpy(), np.array([e.best[0] for e in scal]))
+        assert np.array_equal(env.best_patterns.cpu().numpy(), np.stack([e.best[1] for e in scal]).astype(np.int8))
+        if done.any():
+            env.reset(np.nonzero(done.cpu().numpy())[0])
+            for e, d in zip(scal, done.cpu().numpy()):
+                if d:
+                    e.reset()
+            assert np.array_equal(env.obs().cpu().numpy(), np.stack([e.struct for e in scal]))
+    be.close()
+
+
+def test_stage_timers_and_launch_counter(pkg, torch_mod):
+    torch = torch_mod
+    be = pkg.RCWABatch(256, 40, max_batch=32)
+    pats = torch.from_numpy(np.random.default_rng(0).choice([-1, 1], (64, 256)).astype(np.int8)).cuda()
+    n0 = be.launch_count()
+    be.set_stage_timing(True)
+    be.evaluate(pats)
+    times = be.stage_times()
+    be.set_stage_timing(False)
+    launched = be.launch_count() - n0
+    assert launched == sum(c for _, c in times.values()) > 0
+    assert all(ms > 0 for ms, c in times.values() if c)
+    be.close()
