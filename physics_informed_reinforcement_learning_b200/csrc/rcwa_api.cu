@@ -156,7 +156,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   CUDA_TRY(dmalloc(&h->wstatus, Bc));
 
   // ---- launch plans: matrices go to shared memory when they fit, else to a per-CTA L2-resident spill ----
-  const size_t budget = h->smem_optin;
+  const size_t budget = h->smem_optin - 1024;   // static __shared__ of the kernels counts against the opt-in limit
   const size_t rmat = (size_t)ff * h->ld * sizeof(double), cmat = 2 * rmat;
   {
     size_t vec = (size_t)front_vec_doubles(ff, N, nc) * 8;
@@ -164,7 +164,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->front_smem = vec + h->front_mats * rmat;
     int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / FRONT_NT, budget / std::max<size_t>(h->front_smem + 1024, 1)));
     h->front_grid = h->sm_count * per_sm;
-    CUDA_TRY(cudaFuncSetAttribute(k_front<FRONT_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    CUDA_TRY(cudaFuncSetAttribute(k_front<FRONT_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
   {
     size_t vec = (size_t)tridiag_vec_doubles(ff) * 8;
@@ -172,7 +172,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->tri_smem = vec + h->tri_mats * rmat;
     int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / TRI_NT, budget / std::max<size_t>(h->tri_smem + 1024, 1)));
     h->tri_grid = h->sm_count * per_sm;
-    CUDA_TRY(cudaFuncSetAttribute(k_tridiag<TRI_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    CUDA_TRY(cudaFuncSetAttribute(k_tridiag<TRI_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
   {
     size_t vec = (size_t)tail_vec_doubles(ff) * 8;
@@ -180,19 +180,19 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->tail_smem = vec + h->tail_mats * cmat;
     int per_sm = std::max<size_t>(1, std::min<size_t>(2048 / TAIL_NT, budget / std::max<size_t>(h->tail_smem + 1024, 1)));
     h->tail_grid = h->sm_count * per_sm;
-    if (ff <= 96) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
-    else if (ff <= 128) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
-    else CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    if (ff <= 96) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    else if (ff <= 128) CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    else CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
   {
     h->apply_rows = (ff <= 96) ? 96 : 64;
     h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + (size_t)h->apply_rows * h->ld) * 8;
     if (h->apply_smem > budget) { h->apply_rows = 32; h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + 32 * (size_t)h->ld) * 8; }
-    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
-    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
-    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
     h->ql_smem = (size_t)2 * ff * 32 * 8;
-    CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_optin));
+    CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
   // spill area: sized for the hungriest kernel (tail: Hq + up to 2 complex matrices)
   h->scratch_ctas = std::max(std::max(h->front_grid, h->tri_grid), h->tail_grid);
@@ -278,10 +278,10 @@ extern "C" int pirl_rcwa_stage_times(pirl_handle* h, double* ms, int64_t* launch
 
 extern "C" int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
                               int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status, void* stream) {
+  if (B == 0 && h) return 0;   // empty batch: nothing to do (pointers may be null)
   if (!h || !patterns || !params || !eff) return fail(-1, "null argument");
   if (B < 0) return fail(-2, "negative batch");
   if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
-  if (B == 0) return 0;
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t mb = h->cfg.max_batch;
@@ -298,10 +298,10 @@ extern "C" int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const doub
 extern "C" int pirl_rcwa_eval_host(pirl_handle* h, const int8_t* patterns, const double* params,
                                    int32_t param_stride, int64_t B, double* eff, double* de_r3, double* de_t3,
                                    int32_t* status) {
+  if (B == 0 && h) return 0;   // empty batch: nothing to do (pointers may be null)
   if (!h || !patterns || !params || !eff) return fail(-1, "null argument");
   if (B < 0) return fail(-2, "negative batch");
   if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
-  if (B == 0) return 0;
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   if (B > h->hd_cap) {
     cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);

@@ -273,7 +273,9 @@ def test_vector_env_matches_scalar_semantics_bit_exact(pkg, torch_mod):
         assert np.array_equal(env.best_eff.cpu().numpy(), np.array([e.best[0] for e in scal]))
         assert np.array_equal(env.best_patterns.cpu().numpy(), np.stack([e.best[1] for e in scal]).astype(np.int8))
         if done.any():
+            state = np.random.get_state()            # both sides must consume the SAME global-RNG draws
             env.reset(np.nonzero(done.cpu().numpy())[0])
+            np.random.set_state(state)
             for e, d in zip(scal, done.cpu().numpy()):
                 if d:
                     e.reset()
