@@ -2,10 +2,12 @@
 // Host side only owns: the handle, its device workspaces and two tiny tables.  No torch, no C++ types
 // in the exported signatures.
 #include "rcwa_kernels.cuh"
+#include "rcwa_regtile.cuh"
 #include "../../include/pirl_rcwa.h"
 
 #include <complex>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <utility>
@@ -46,6 +48,7 @@ struct pirl_handle {
   int tail_grid, tail_mats; size_t tail_smem;
   int apply_rows; size_t apply_smem;
   size_t ql_smem;
+  bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
   // host staging for eval_host
@@ -58,8 +61,11 @@ struct pirl_handle {
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
 };
 
-static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail"};
-static constexpr int kNumStages = 5;
+static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front"};
+static constexpr int kNumStages = 6;
+
+// register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
+using Cfg81 = TileCfg<81, 9, 9, 9, 9, 2>;
 
 static cudaEvent_t take_event(pirl_handle* h) {
   if (!h->ev_free.empty()) { cudaEvent_t e = h->ev_free.back(); h->ev_free.pop_back(); return e; }
@@ -194,6 +200,15 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
+  if (ff == Cfg81::FF && !getenv("PIRL_NO_REGTILE")) {
+    h->regtile = true;
+    h->rk_front_smem = (size_t)FrontSmem<Cfg81>::doubles(nc) * 8;
+    CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    int per_sm = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_front<Cfg81>, Cfg81::NT, h->rk_front_smem));
+    if (per_sm < 1) return fail(-9, "rk_front does not fit on this device");
+    h->rk_front_grid = h->sm_count * per_sm;
+  }
   // spill area: sized for the hungriest kernel (tail: Hq + up to 2 complex matrices)
   h->scratch_ctas = std::max(std::max(h->front_grid, h->tri_grid), h->tail_grid);
   h->scratch_stride = 2 * m2 + 2 * (2 * (size_t)ff * h->ld) + 16;
@@ -229,10 +244,16 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   P.scratch = h->scratch; P.scratch_stride = h->scratch_stride;
   P.eff = eff; P.de_r3 = de_r3; P.de_t3 = de_t3; P.status = status;
 
-  P.smem_mats = h->front_mats;
-  { StageTimer t(h, 0, st); k_front<FRONT_NT><<<std::min(Bc, h->front_grid), FRONT_NT, h->front_smem, st>>>(P); }
-  P.smem_mats = h->tri_mats;
-  { StageTimer t(h, 1, st); k_tridiag<TRI_NT><<<std::min(Bc, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P); }
+  if (h->regtile) {
+    StageTimer t(h, 5, st);
+    rk_front<Cfg81><<<std::min(Bc, h->rk_front_grid), Cfg81::NT, h->rk_front_smem, st>>>(P);
+    h->launches -= 1;
+  } else {
+    P.smem_mats = h->front_mats;
+    { StageTimer t(h, 0, st); k_front<FRONT_NT><<<std::min(Bc, h->front_grid), FRONT_NT, h->front_smem, st>>>(P); }
+    P.smem_mats = h->tri_mats;
+    { StageTimer t(h, 1, st); k_tridiag<TRI_NT><<<std::min(Bc, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P); }
+  }
   { StageTimer t(h, 2, st); k_ql<<<(Bc + 31) / 32, 32, h->ql_smem, st>>>(P); }
   {
     StageTimer t(h, 3, st);

@@ -86,7 +86,7 @@ __device__ __forceinline__ cplx warp_sum(cplx v) {
 // ---------------------------------------------------------------------------------------------------
 // shared-memory layouts (host and device use the same functions)
 // ---------------------------------------------------------------------------------------------------
-__host__ __device__ inline int pirl_even(int x) { return (x + 1) & ~1; }
+__host__ __device__ constexpr int pirl_even(int x) { return (x + 1) & ~1; }
 // k_front: cre, cim [2N+1 each], rowk, colk, dinv [ff each], pattern bytes
 __host__ __device__ inline int front_vec_doubles(int ff, int N, int n_cells) {
   return pirl_even(2 * (2 * N + 1) + 3 * ff + (n_cells + 7) / 8);
