@@ -48,6 +48,7 @@ STAGE_FLOPS_FF3 = {
     "k_apply": 12.0,                           # rotations applied to the ff x ff basis (steqr with vectors)
     "k_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
     "rk_front": 28.0 / 3.0 + 44.0 / 3.0,       # register-tile fusion of k_front + k_tridiag
+    "rk_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
     "k_solve": 220.0 / 3.0,                    # fused whole-path kernel
 }
 

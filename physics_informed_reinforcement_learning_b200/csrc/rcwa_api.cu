@@ -48,7 +48,8 @@ struct pirl_handle {
   int tail_grid, tail_mats; size_t tail_smem;
   int apply_rows; size_t apply_smem;
   size_t ql_smem;
-  bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0;
+  unsigned long long* phase_clk = nullptr;   // [32] device counters (PIRL_PHASE_CLOCKS=1)
+  bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
   // host staging for eval_host
@@ -61,11 +62,13 @@ struct pirl_handle {
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
 };
 
-static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front"};
-static constexpr int kNumStages = 6;
+static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail"};
+static constexpr int kNumStages = 7;
 
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
-using Cfg81 = TileCfg<81, 9, 9, 9, 9, 2>;
+using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2>;
+using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
+static constexpr int kTailMmax = 72;
 
 static cudaEvent_t take_event(pirl_handle* h) {
   if (!h->ev_free.empty()) { cudaEvent_t e = h->ev_free.back(); h->ev_free.pop_back(); return e; }
@@ -208,6 +211,15 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_front<Cfg81>, Cfg81::NT, h->rk_front_smem));
     if (per_sm < 1) return fail(-9, "rk_front does not fit on this device");
     h->rk_front_grid = h->sm_count * per_sm;
+    h->rk_tail_smem = (size_t)TailSmem<Cfg81T, kTailMmax>::doubles * 8;
+    CUDA_TRY(cudaFuncSetAttribute(rk_tail<Cfg81T, kTailMmax>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_tail<Cfg81T, kTailMmax>, Cfg81T::NT, h->rk_tail_smem));
+    if (per_sm < 1) return fail(-9, "rk_tail does not fit on this device");
+    h->rk_tail_grid = h->sm_count * per_sm;
+  }
+  if (getenv("PIRL_PHASE_CLOCKS")) {
+    CUDA_TRY(dmalloc(&h->phase_clk, 32));
+    CUDA_TRY(cudaMemset(h->phase_clk, 0, 32 * sizeof(unsigned long long)));
   }
   // spill area: sized for the hungriest kernel (tail: Hq + up to 2 complex matrices)
   h->scratch_ctas = std::max(std::max(h->front_grid, h->tri_grid), h->tail_grid);
@@ -223,7 +235,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaSetDevice(h->cfg.device);
   cudaFree(h->d_tw); cudaFree(h->d_Dk);
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
-  cudaFree(h->rot_cs); cudaFree(h->rot_col); cudaFree(h->nrot); cudaFree(h->wstatus); cudaFree(h->scratch);
+  cudaFree(h->rot_cs); cudaFree(h->rot_col); cudaFree(h->nrot); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk);
   cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto& p : h->ev_pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
@@ -240,7 +252,7 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   P.n_inc = h->cfg.n_inc; P.n_exit = h->cfg.n_exit; P.eps_g = h->cfg.n_groove * h->cfg.n_groove;
   P.tw = h->d_tw; P.Dk = h->d_Dk; P.patterns = patterns; P.params = params; P.pstride = pstride;
   P.Cbuf = h->Cbuf; P.Lbuf = h->Lbuf; P.Wbuf = h->Wbuf; P.tri = h->tri; P.lam = h->lam;
-  P.rot_cs = h->rot_cs; P.rot_col = h->rot_col; P.nrot = h->nrot; P.maxrot = h->maxrot; P.wstatus = h->wstatus;
+  P.rot_cs = h->rot_cs; P.rot_col = h->rot_col; P.nrot = h->nrot; P.maxrot = h->maxrot; P.wstatus = h->wstatus; P.phase_clk = h->phase_clk;
   P.scratch = h->scratch; P.scratch_stride = h->scratch_stride;
   P.eff = eff; P.de_r3 = de_r3; P.de_t3 = de_t3; P.status = status;
 
@@ -261,6 +273,12 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
     if (h->apply_rows == 96) k_apply<96><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 64) k_apply<64><<<g, 64, h->apply_smem, st>>>(P);
     else k_apply<32><<<g, 32, h->apply_smem, st>>>(P);
+  }
+  if (h->regtile && !getenv("PIRL_NO_RKTAIL")) {
+    StageTimer t(h, 6, st);
+    rk_tail<Cfg81T, kTailMmax><<<std::min(Bc, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
+    P.fallback_only = 1;
+    h->launches += 1;
   }
   P.smem_mats = h->tail_mats;
   const int tg = std::min(Bc, h->tail_grid);
@@ -389,6 +407,14 @@ extern "C" int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, 
       std::vector<int> tmp(B);
       CUDA_TRY(cudaMemcpy(tmp.data(), h->nrot, B * sizeof(int), cudaMemcpyDeviceToHost));
       for (size_t i = 0; i < B && (int64_t)i < max_elems; ++i) dst[i] = (double)tmp[i];
+      return 0;
+    }
+    case 5: {   // per-phase clock accumulators (32 values), then reset
+      if (!h->phase_clk) return fail(-3, "phase clocks not enabled (PIRL_PHASE_CLOCKS=1)");
+      unsigned long long tmp[32];
+      CUDA_TRY(cudaMemcpy(tmp, h->phase_clk, sizeof(tmp), cudaMemcpyDeviceToHost));
+      CUDA_TRY(cudaMemset(h->phase_clk, 0, sizeof(tmp)));
+      for (int i = 0; i < 32 && i < max_elems; ++i) dst[i] = (double)tmp[i];
       return 0;
     }
     default: return fail(-2, "unknown debug item");

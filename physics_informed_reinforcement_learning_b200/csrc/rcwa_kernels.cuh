@@ -37,6 +37,8 @@ struct KParams {
   int* nrot;                  // [B]
   int maxrot;
   int* wstatus;               // [B] working status bits
+  int fallback_only;          // k_tail: process only structures flagged by rk_tail (PIRL_ST_TAIL_FALLBACK)
+  unsigned long long* phase_clk;  // optional [32] per-phase clock64 accumulators (debug / profiling), may be null
   double* scratch;            // per-CTA spill area for matrices that do not fit in shared memory
   size_t scratch_stride;      // doubles per CTA
   int smem_mats;              // how many (kernel-specific) matrices live in shared memory
@@ -533,6 +535,7 @@ __global__ void __launch_bounds__(NT) k_tail(KParams P) {
   double* Wr = reinterpret_cast<double*>(Sm);                   // W staged in S's storage (real, ld)
 
   for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
+    if (P.fallback_only && !(P.wstatus[b] & 0x100)) continue;   // uniform per CTA
     __syncthreads();
     const double* pr = P.params + (size_t)b * P.pstride;
     const double wl = pr[0], ang = pr[1], thick = pr[2];
@@ -724,7 +727,7 @@ __global__ void __launch_bounds__(NT) k_tail(KParams P) {
       det[0] = (Tm.x * Tm.x + Tm.y * Tm.y) * k1II / (nII * nII) * nI;
       det[1] = (T0.x * T0.x + T0.y * T0.y) * nI / nII;
       det[2] = (Tp.x * Tp.x + Tp.y * Tp.y) * k1II / (nII * nII) * nI;
-      int st = P.wstatus[b];
+      int st = P.wstatus[b] & 0xff;
       if (!isfinite(det[0]) || !isfinite(det[1]) || !isfinite(der[1])) st |= PIRL_ST_NONFINITE_;
       P.eff[b] = det[0];
       if (P.de_r3) { P.de_r3[3 * b] = der[0]; P.de_r3[3 * b + 1] = der[1]; P.de_r3[3 * b + 2] = der[2]; }
