@@ -37,8 +37,14 @@ struct pirl_handle {
   // chunk workspaces
   double *Cbuf = nullptr, *Lbuf = nullptr, *Wbuf = nullptr, *tri = nullptr, *lam = nullptr;
   cplx* rot_cs = nullptr;
-  uint8_t* rot_col = nullptr;
-  int *nrot = nullptr, *wstatus = nullptr;
+  uint16_t* sweeps = nullptr;
+  int *nrot = nullptr, *nsw = nullptr, *wstatus = nullptr;
+  int maxsw = 0;
+  // sub-chunk pipeline: the latency-bound QL kernel of sub-chunk c runs on a side stream under the front kernels of c+1...
+  static constexpr int kMaxSub = 16, kSide = 4;
+  cudaStream_t side[kSide] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t evF[kMaxSub] = {}, evQ[kMaxSub] = {};
+  int sub_size = 0;
   double* scratch = nullptr;
   size_t scratch_stride = 0;
   int scratch_ctas = 0;
@@ -49,6 +55,8 @@ struct pirl_handle {
   int apply_rows; size_t apply_smem;
   size_t ql_smem;
   unsigned long long* phase_clk = nullptr;   // [32] device counters (PIRL_PHASE_CLOCKS=1)
+  unsigned long long* trace = nullptr;       // CTA trace records (PIRL_TRACE=1)
+  bool no_rktail = false;
   bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
@@ -68,7 +76,7 @@ static constexpr int kNumStages = 7;
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
 using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2>;
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
-static constexpr int kTailMmax = 72;
+static constexpr int kTailMmax = 64;   // 64 keeps rk_tail + one k_ql CTA within one SM's shared memory
 
 static cudaEvent_t take_event(pirl_handle* h) {
   if (!h->ev_free.empty()) { cudaEvent_t e = h->ev_free.back(); h->ev_free.pop_back(); return e; }
@@ -95,6 +103,13 @@ static constexpr int TAIL_NT = 512;
 
 template <typename T>
 static cudaError_t dmalloc(T** p, size_t n) { return cudaMalloc((void**)p, n * sizeof(T)); }
+
+// every kernel asks for the maximum shared-memory carveout: kernels with different carveouts cannot share an SM, and the
+// sub-chunk pipeline relies on k_ql CTAs running beside the front / back kernels
+template <typename K>
+static cudaError_t max_carveout(K kern) {
+  return cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+}
 
 // how many matrices of `mat_bytes` fit beside `vec_bytes` in `budget` (capped at want)
 static int mats_that_fit(size_t budget, size_t vec_bytes, size_t mat_bytes, int want) {
@@ -160,8 +175,10 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   CUDA_TRY(dmalloc(&h->tri, Bc * 2 * ff));
   CUDA_TRY(dmalloc(&h->lam, Bc * ff));
   CUDA_TRY(dmalloc(&h->rot_cs, Bc * h->maxrot));
-  CUDA_TRY(dmalloc(&h->rot_col, Bc * h->maxrot));
+  h->maxsw = 16 * ff;
+  CUDA_TRY(dmalloc(&h->sweeps, Bc * h->maxsw));
   CUDA_TRY(dmalloc(&h->nrot, Bc));
+  CUDA_TRY(dmalloc(&h->nsw, Bc));
   CUDA_TRY(dmalloc(&h->wstatus, Bc));
 
   // ---- launch plans: matrices go to shared memory when they fit, else to a per-CTA L2-resident spill ----
@@ -195,11 +212,12 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   }
   {
     h->apply_rows = (ff <= 96) ? 96 : 64;
-    h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + (size_t)h->apply_rows * h->ld) * 8;
-    if (h->apply_smem > budget) { h->apply_rows = 32; h->apply_smem = (size_t)(2 * APPLY_CHUNK + APPLY_CHUNK / 2 + 32 * (size_t)h->ld) * 8; }
-    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
-    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
-    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    const size_t apply_budget = budget - 2 * APPLY_CHUNK * sizeof(cplx);   // static rotation buffers of k_apply
+    h->apply_smem = (size_t)std::min(h->apply_rows, ff) * h->ld * 8;
+    if (h->apply_smem > apply_budget) { h->apply_rows = 32; h->apply_smem = 32 * (size_t)h->ld * 8; }
+    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_budget));
+    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_budget));
+    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_budget));
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
@@ -217,6 +235,14 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     if (per_sm < 1) return fail(-9, "rk_tail does not fit on this device");
     h->rk_tail_grid = h->sm_count * per_sm;
   }
+  CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
+  CUDA_TRY(max_carveout(k_apply<96>)); CUDA_TRY(max_carveout(k_apply<64>)); CUDA_TRY(max_carveout(k_apply<32>));
+  CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
+  CUDA_TRY(max_carveout(rk_front<Cfg81>)); CUDA_TRY(max_carveout(rk_tail<Cfg81T, kTailMmax>));
+  if (getenv("PIRL_TRACE")) {
+    CUDA_TRY(dmalloc(&h->trace, 1 + 4 * (size_t)PIRL_TRACE_CAP));
+    CUDA_TRY(cudaMemset(h->trace, 0, sizeof(unsigned long long)));
+  }
   if (getenv("PIRL_PHASE_CLOCKS")) {
     CUDA_TRY(dmalloc(&h->phase_clk, 32));
     CUDA_TRY(cudaMemset(h->phase_clk, 0, 32 * sizeof(unsigned long long)));
@@ -226,6 +252,21 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   h->scratch_stride = 2 * m2 + 2 * (2 * (size_t)ff * h->ld) + 16;
   CUDA_TRY(dmalloc(&h->scratch, (size_t)h->scratch_ctas * h->scratch_stride));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  {
+    int lo = 0, hi = 0;
+    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    for (int i = 0; i < pirl_handle::kSide; ++i) CUDA_TRY(cudaStreamCreateWithPriority(&h->side[i], cudaStreamNonBlocking, hi));
+    for (int i = 0; i < pirl_handle::kMaxSub; ++i) {
+      CUDA_TRY(cudaEventCreateWithFlags(&h->evF[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&h->evQ[i], cudaEventDisableTiming));
+    }
+    // sub-chunk pipeline: off by default (PIRL_SUBCHUNK=<structures per sub-chunk> enables it).  Measured with the CTA trace
+    // (tools/cta_trace.py, profiles/r01h_cta_trace_subchunk592.txt): persistent front / tail grids sized to the whole machine
+    // leave straggler waves when k_ql CTAs hold SM slots, so the overlap loses more than it hides.
+    h->sub_size = 0;
+    if (const char* e = getenv("PIRL_SUBCHUNK")) h->sub_size = atoi(e);
+    h->no_rktail = getenv("PIRL_NO_RKTAIL") != nullptr;
+  }
   *out = h;
   return 0;
 }
@@ -235,13 +276,78 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaSetDevice(h->cfg.device);
   cudaFree(h->d_tw); cudaFree(h->d_Dk);
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
-  cudaFree(h->rot_cs); cudaFree(h->rot_col); cudaFree(h->nrot); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk);
+  cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace);
   cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  for (auto q : h->side) if (q) cudaStreamDestroy(q);
+  for (auto e : h->evF) if (e) cudaEventDestroy(e);
+  for (auto e : h->evQ) if (e) cudaEventDestroy(e);
   for (auto& p : h->ev_pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
   for (auto e : h->ev_free) cudaEventDestroy(e);
   delete h;
   return 0;
+}
+
+// kernel parameters of the sub-chunk [off, off + cnt) of a chunk whose first structure has index 0 in the workspaces
+static KParams sub_params(const KParams& P0, int n_cells, int ff, int off, int cnt) {
+  KParams P = P0;
+  const size_t m2 = (size_t)ff * ff;
+  P.B = cnt;
+  P.patterns += (size_t)off * n_cells;
+  P.params += (size_t)off * P.pstride;
+  P.Cbuf += off * m2; P.Lbuf += off * m2; P.Wbuf += off * m2;
+  P.tri += (size_t)off * 2 * ff; P.lam += (size_t)off * ff;
+  P.rot_cs += (size_t)off * P.maxrot; P.sweeps += (size_t)off * P.maxsw;
+  P.nrot += off; P.nsw += off; P.wstatus += off;
+  P.eff += off;
+  if (P.de_r3) P.de_r3 += 3 * (size_t)off;
+  if (P.de_t3) P.de_t3 += 3 * (size_t)off;
+  if (P.status) P.status += off;
+  return P;
+}
+
+static void launch_front(pirl_handle* h, KParams P, cudaStream_t st) {
+  if (h->regtile) {
+    StageTimer t(h, 5, st);
+    rk_front<Cfg81><<<std::min(P.B, h->rk_front_grid), Cfg81::NT, h->rk_front_smem, st>>>(P);
+    h->launches += 1;
+  } else {
+    P.smem_mats = h->front_mats;
+    { StageTimer t(h, 0, st); k_front<FRONT_NT><<<std::min(P.B, h->front_grid), FRONT_NT, h->front_smem, st>>>(P); }
+    P.smem_mats = h->tri_mats;
+    { StageTimer t(h, 1, st); k_tridiag<TRI_NT><<<std::min(P.B, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P); }
+    h->launches += 2;
+  }
+}
+
+static void launch_ql(pirl_handle* h, const KParams& P, cudaStream_t st) {
+  StageTimer t(h, 2, st);
+  k_ql<<<(P.B + 31) / 32, 32, h->ql_smem, st>>>(P);
+  h->launches += 1;
+}
+
+static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
+  {
+    StageTimer t(h, 3, st);
+    dim3 g(P.B, (h->ff + h->apply_rows - 1) / h->apply_rows);
+    if (h->apply_rows == 96) k_apply<96><<<g, 96, h->apply_smem, st>>>(P);
+    else if (h->apply_rows == 64) k_apply<64><<<g, 64, h->apply_smem, st>>>(P);
+    else k_apply<32><<<g, 32, h->apply_smem, st>>>(P);
+    h->launches += 1;
+  }
+  if (h->regtile && !h->no_rktail) {
+    StageTimer t(h, 6, st);
+    rk_tail<Cfg81T, kTailMmax><<<std::min(P.B, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
+    P.fallback_only = 1;
+    h->launches += 1;
+  }
+  P.smem_mats = h->tail_mats;
+  const int tg = std::min(P.B, h->tail_grid);
+  StageTimer t(h, 4, st);
+  if (h->ff <= 96) k_tail<TAIL_NT, 3><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
+  else if (h->ff <= 128) k_tail<TAIL_NT, 4><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
+  else k_tail<TAIL_NT, 8><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
+  h->launches += 1;
 }
 
 static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
@@ -252,41 +358,40 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   P.n_inc = h->cfg.n_inc; P.n_exit = h->cfg.n_exit; P.eps_g = h->cfg.n_groove * h->cfg.n_groove;
   P.tw = h->d_tw; P.Dk = h->d_Dk; P.patterns = patterns; P.params = params; P.pstride = pstride;
   P.Cbuf = h->Cbuf; P.Lbuf = h->Lbuf; P.Wbuf = h->Wbuf; P.tri = h->tri; P.lam = h->lam;
-  P.rot_cs = h->rot_cs; P.rot_col = h->rot_col; P.nrot = h->nrot; P.maxrot = h->maxrot; P.wstatus = h->wstatus; P.phase_clk = h->phase_clk;
+  P.rot_cs = h->rot_cs; P.sweeps = h->sweeps; P.nrot = h->nrot; P.nsw = h->nsw; P.maxrot = h->maxrot; P.maxsw = h->maxsw;
+  P.wstatus = h->wstatus; P.phase_clk = h->phase_clk; P.trace = h->trace;
   P.scratch = h->scratch; P.scratch_stride = h->scratch_stride;
   P.eff = eff; P.de_r3 = de_r3; P.de_t3 = de_t3; P.status = status;
 
-  if (h->regtile) {
-    StageTimer t(h, 5, st);
-    rk_front<Cfg81><<<std::min(Bc, h->rk_front_grid), Cfg81::NT, h->rk_front_smem, st>>>(P);
-    h->launches -= 1;
+  // Sub-chunk pipeline.  k_ql is one thread per structure and purely latency bound (about 3 ms whatever the batch), so a
+  // chunk is cut into sub-chunks: all front kernels are issued first on the caller's stream, each sub-chunk's k_ql runs on
+  // a high-priority side stream as soon as its front kernel is done (under the following front / back kernels), and the
+  // back kernels (k_apply, tail) follow on the caller's stream, each waiting for its own k_ql.
+  const int sub = h->sub_size;
+  int nsub = (sub > 0) ? (Bc + sub - 1) / sub : 1;
+  if (nsub > pirl_handle::kMaxSub) nsub = pirl_handle::kMaxSub;
+  if (nsub <= 1) {
+    launch_front(h, P, st);
+    launch_ql(h, P, st);
+    launch_back(h, P, st);
   } else {
-    P.smem_mats = h->front_mats;
-    { StageTimer t(h, 0, st); k_front<FRONT_NT><<<std::min(Bc, h->front_grid), FRONT_NT, h->front_smem, st>>>(P); }
-    P.smem_mats = h->tri_mats;
-    { StageTimer t(h, 1, st); k_tridiag<TRI_NT><<<std::min(Bc, h->tri_grid), TRI_NT, h->tri_smem, st>>>(P); }
+    const int per = (sub * nsub >= Bc) ? sub : (Bc + nsub - 1) / nsub;
+    KParams Ps[pirl_handle::kMaxSub];
+    for (int c = 0; c < nsub; ++c) {
+      const int off = c * per, cnt = std::min(per, Bc - off);
+      Ps[c] = sub_params(P, h->cfg.n_cells, h->ff, off, cnt);
+      launch_front(h, Ps[c], st);
+      CUDA_TRY(cudaEventRecord(h->evF[c], st));
+      cudaStream_t qs = h->side[c % pirl_handle::kSide];
+      CUDA_TRY(cudaStreamWaitEvent(qs, h->evF[c], 0));
+      launch_ql(h, Ps[c], qs);
+      CUDA_TRY(cudaEventRecord(h->evQ[c], qs));
+    }
+    for (int c = 0; c < nsub; ++c) {
+      CUDA_TRY(cudaStreamWaitEvent(st, h->evQ[c], 0));
+      launch_back(h, Ps[c], st);
+    }
   }
-  { StageTimer t(h, 2, st); k_ql<<<(Bc + 31) / 32, 32, h->ql_smem, st>>>(P); }
-  {
-    StageTimer t(h, 3, st);
-    dim3 g(Bc, (h->ff + h->apply_rows - 1) / h->apply_rows);
-    if (h->apply_rows == 96) k_apply<96><<<g, 96, h->apply_smem, st>>>(P);
-    else if (h->apply_rows == 64) k_apply<64><<<g, 64, h->apply_smem, st>>>(P);
-    else k_apply<32><<<g, 32, h->apply_smem, st>>>(P);
-  }
-  if (h->regtile && !getenv("PIRL_NO_RKTAIL")) {
-    StageTimer t(h, 6, st);
-    rk_tail<Cfg81T, kTailMmax><<<std::min(Bc, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
-    P.fallback_only = 1;
-    h->launches += 1;
-  }
-  P.smem_mats = h->tail_mats;
-  const int tg = std::min(Bc, h->tail_grid);
-  StageTimer t(h, 4, st);
-  if (h->ff <= 96) k_tail<TAIL_NT, 3><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
-  else if (h->ff <= 128) k_tail<TAIL_NT, 4><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
-  else k_tail<TAIL_NT, 8><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
-  h->launches += 5;
   h->last_chunk = Bc;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -415,6 +520,17 @@ extern "C" int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, 
       CUDA_TRY(cudaMemcpy(tmp, h->phase_clk, sizeof(tmp), cudaMemcpyDeviceToHost));
       CUDA_TRY(cudaMemset(h->phase_clk, 0, sizeof(tmp)));
       for (int i = 0; i < 32 && i < max_elems; ++i) dst[i] = (double)tmp[i];
+      return 0;
+    }
+    case 6: {   // CTA trace: raw 64-bit words (counter, then 4 words per record) copied into dst, then reset
+      if (!h->trace) return fail(-3, "CTA trace not enabled (PIRL_TRACE=1)");
+      unsigned long long cnt = 0;
+      CUDA_TRY(cudaMemcpy(&cnt, h->trace, sizeof(cnt), cudaMemcpyDeviceToHost));
+      if (cnt > PIRL_TRACE_CAP) cnt = PIRL_TRACE_CAP;
+      size_t words = 1 + 4 * (size_t)cnt;
+      if ((int64_t)words > max_elems) words = (size_t)max_elems;
+      CUDA_TRY(cudaMemcpy(dst, h->trace, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+      CUDA_TRY(cudaMemset(h->trace, 0, sizeof(unsigned long long)));
       return 0;
     }
     default: return fail(-2, "unknown debug item");

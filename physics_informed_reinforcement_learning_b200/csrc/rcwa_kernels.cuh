@@ -33,12 +33,15 @@ struct KParams {
   double* tri;                // [B][2][ff]
   double* lam;                // [B][ff]
   cplx* rot_cs;               // [B][maxrot]
-  uint8_t* rot_col;           // [B][maxrot]
+  uint16_t* sweeps;           // [B][maxsw]  QL sweep descriptors: first column | rotation count << 8
+  int* nsw;                   // [B]
+  int maxsw;
   int* nrot;                  // [B]
   int maxrot;
   int* wstatus;               // [B] working status bits
   int fallback_only;          // k_tail: process only structures flagged by rk_tail (PIRL_ST_TAIL_FALLBACK)
   unsigned long long* phase_clk;  // optional [32] per-phase clock64 accumulators (debug / profiling), may be null
+  unsigned long long* trace;      // optional CTA trace (PIRL_TRACE=1): [0] = record counter, then records of 4 words
   double* scratch;            // per-CTA spill area for matrices that do not fit in shared memory
   size_t scratch_stride;      // doubles per CTA
   int smem_mats;              // how many (kernel-specific) matrices live in shared memory
@@ -70,6 +73,33 @@ __device__ __forceinline__ cplx cinv(cplx a) {
 __device__ __forceinline__ cplx cadd(cplx a, cplx b) { return make_double2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ cplx csub(cplx a, cplx b) { return make_double2(a.x - b.x, a.y - b.y); }
 __device__ __forceinline__ cplx cscale(cplx a, double s) { return make_double2(a.x * s, a.y * s); }
+
+// ---- CTA trace (poor man's timeline; there is no nsys on the box): kernel id, SM id, start / end in globaltimer ns ----
+#define PIRL_TRACE_CAP (1 << 20)
+__device__ __forceinline__ unsigned long long pirl_gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned pirl_smid() {
+  unsigned s;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
+  return s;
+}
+struct CtaTrace {
+  unsigned long long t0;
+  __device__ __forceinline__ CtaTrace(const unsigned long long* tr) : t0(tr ? pirl_gtime() : 0ull) {}
+  __device__ __forceinline__ void done(unsigned long long* tr, int kernel_id, int first) const {
+    if (!tr || threadIdx.x != 0) return;
+    const unsigned long long slot = atomicAdd(tr, 1ull);
+    if (slot >= PIRL_TRACE_CAP) return;
+    unsigned long long* r = tr + 1 + 4 * slot;
+    r[0] = ((unsigned long long)kernel_id << 32) | pirl_smid();
+    r[1] = ((unsigned long long)blockIdx.x << 32) | (unsigned)first;
+    r[2] = t0;
+    r[3] = pirl_gtime();
+  }
+};
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -385,11 +415,14 @@ __global__ void __launch_bounds__(NT) k_tridiag(KParams P) {
 //   Only the scalar recurrences run here (latency bound, all structures in flight at once); the O(n^3)
 //   part -- applying the rotations to the n x n basis -- is k_apply.  d/e live in shared memory,
 //   lane-interleaved so that divergent positions never bank-conflict.
+//   Output stream: rotations (c, s) in application order, plus one descriptor per QL sweep
+//   (first column hi, rotation count): a sweep rotates columns (hi, hi+1), (hi-1, hi), ... in that order.
 // ===================================================================================================
 __global__ void __launch_bounds__(32) k_ql(KParams P) {
   extern __shared__ __align__(16) double sm[];
   const int ff = P.ff, lane = threadIdx.x;
   const int b = blockIdx.x * 32 + lane;
+  const CtaTrace trc(P.trace);
   if (b >= P.B) return;
   double* d = sm + lane;              // d[i] at d[i*32]
   double* e = sm + (size_t)ff * 32 + lane;
@@ -397,8 +430,8 @@ __global__ void __launch_bounds__(32) k_ql(KParams P) {
   for (int i = 0; i < ff; ++i) { d[i * 32] = tg[i]; e[i * 32] = tg[ff + i]; }
   e[(ff - 1) * 32] = 0.0;
   cplx* rc = P.rot_cs + (size_t)b * P.maxrot;
-  uint8_t* rcol = P.rot_col + (size_t)b * P.maxrot;
-  int nrot = 0;
+  uint16_t* sw = P.sweeps + (size_t)b * P.maxsw;
+  int nrot = 0, nsw = 0;
   bool ok = true;
   const double eps = 2.220446049250313e-16;
   for (int l = 0; l < ff; ++l) {
@@ -418,19 +451,22 @@ __global__ void __launch_bounds__(32) k_ql(KParams P) {
       g = d[m * 32] - dl + el / (g + copysign(r, g));
       double s = 1.0, c = 1.0, p = 0.0;
       int i = m - 1;
+      const int hi = i;
+      int cnt = 0;
       bool underflow = false;
       for (; i >= l; --i) {
         const double ei = e[i * 32];
         const double f = s * ei, bb = c * ei;
-        r = sqrt(fma(f, f, g * g));
-        e[(i + 1) * 32] = r;
-        if (r == 0.0) {
+        const double h = fma(f, f, g * g);
+        if (h == 0.0) {
+          e[(i + 1) * 32] = 0.0;
           d[(i + 1) * 32] -= p;
           e[m * 32] = 0.0;
           underflow = true;
           break;
         }
-        const double rinv = 1.0 / r;
+        const double rinv = rsqrt(h);      // one reciprocal square root instead of sqrt + divide on the critical path
+        e[(i + 1) * 32] = h * rinv;
         s = f * rinv;
         c = g * rinv;
         g = d[(i + 1) * 32] - p;
@@ -438,9 +474,10 @@ __global__ void __launch_bounds__(32) k_ql(KParams P) {
         p = s * r;
         d[(i + 1) * 32] = g + p;
         g = fma(c, r, -bb);
-        if (nrot < P.maxrot) { rc[nrot] = make_double2(c, s); rcol[nrot] = (uint8_t)i; }
-        ++nrot;
+        if (nrot < P.maxrot) rc[nrot] = make_double2(c, s);
+        ++nrot; ++cnt;
       }
+      if (cnt) { if (nsw < P.maxsw) sw[nsw] = (uint16_t)(hi | (cnt << 8)); ++nsw; }
       if (underflow) continue;
       d[l * 32] -= p;
       e[l * 32] = g;
@@ -449,54 +486,97 @@ __global__ void __launch_bounds__(32) k_ql(KParams P) {
     if (!ok) break;
   }
   if (nrot > P.maxrot) { ok = false; nrot = P.maxrot; }
+  if (nsw > P.maxsw) { ok = false; nsw = 0; nrot = 0; }
   double* lg = P.lam + (size_t)b * ff;
   for (int i = 0; i < ff; ++i) lg[i] = d[i * 32];
   P.nrot[b] = nrot;
+  P.nsw[b] = nsw;
   if (!ok) atomicOr(&P.wstatus[b], PIRL_ST_EIG);
+  __syncwarp();
+  trc.done(P.trace, 2, b);
 }
 
 // ===================================================================================================
-// k_apply : W = M0 * G_1 * G_2 * ...   (each thread owns one row; rotations streamed through smem)
+// k_apply : W = M0 * G_1 * G_2 * ...   Each thread owns one row of the basis in shared memory.  Within a QL sweep
+//   consecutive rotations share a column, so the shared value is carried in a register: one shared load, one shared
+//   store and a single dependent DFMA per rotation.  Rotations are staged through a double-buffered static shared
+//   array (distinct object from the rows: the compiler may hoist the loads of an unrolled group).
 // ===================================================================================================
-#define APPLY_CHUNK 512
+#define APPLY_CHUNK 256
 template <int ROWS>
 __global__ void __launch_bounds__(ROWS) k_apply(KParams P) {
-  extern __shared__ __align__(16) double sm[];
+  extern __shared__ __align__(16) double Z[];
+  __shared__ cplx ccs[2][APPLY_CHUNK];
   const int ff = P.ff, ld = P.ld, tid = threadIdx.x;
   const int b = blockIdx.x, r0 = blockIdx.y * ROWS;
   const int rows = min(ROWS, ff - r0);
-  cplx* ccs = reinterpret_cast<cplx*>(sm);
-  int* ccol = reinterpret_cast<int*>(ccs + APPLY_CHUNK);
-  double* Z = sm + 2 * APPLY_CHUNK + APPLY_CHUNK / 2;
+  const CtaTrace trc(P.trace);
   double* Wg = P.Wbuf + (size_t)b * ff * ff + (size_t)r0 * ff;
   for (int idx = tid; idx < rows * ff; idx += ROWS) {
     int rr = idx / ff, cc = idx - rr * ff;
     Z[rr * ld + cc] = Wg[idx];
   }
-  const int nr = P.nrot[b];
+  const int nr = min(P.nrot[b], P.maxrot);
+  const int nsw = min(P.nsw[b], P.maxsw);
   const cplx* rc = P.rot_cs + (size_t)b * P.maxrot;
-  const uint8_t* rcol = P.rot_col + (size_t)b * P.maxrot;
-  double* zr = Z + tid * ld;
-  for (int base = 0; base < nr; base += APPLY_CHUNK) {
+  const uint16_t* sw = P.sweeps + (size_t)b * P.maxsw;
+  for (int t = tid; t < min(APPLY_CHUNK, nr); t += ROWS) ccs[0][t] = rc[t];
+  __syncthreads();
+  constexpr int PRE = (APPLY_CHUNK + ROWS - 1) / ROWS;
+  double* zr = Z + (tid < rows ? tid : 0) * ld;
+  double* zp = zr;
+  double zc = 0.0;
+  int s = 0, rem = 0;
+  unsigned wnext = (nsw > 0) ? sw[0] : 0u;
+  int buf = 0;
+  for (int base = 0; base < nr; base += APPLY_CHUNK, buf ^= 1) {
     const int cnt = min(APPLY_CHUNK, nr - base);
-    __syncthreads();
-    for (int t = tid; t < cnt; t += ROWS) { ccs[t] = rc[base + t]; ccol[t] = rcol[base + t]; }
-    __syncthreads();
+    const int nb = base + APPLY_CHUNK;
+    cplx pre[PRE];
+#pragma unroll
+    for (int q = 0; q < PRE; ++q) {
+      const int idx = tid + q * ROWS;
+      if (idx < APPLY_CHUNK && nb + idx < nr) pre[q] = rc[nb + idx];
+    }
     if (tid < rows) {
-      for (int t = 0; t < cnt; ++t) {
-        const cplx cs = ccs[t];
-        const int i = ccol[t];
-        const double zi = zr[i], zi1 = zr[i + 1];
-        zr[i + 1] = fma(cs.y, zi, cs.x * zi1);
-        zr[i] = fma(cs.x, zi, -cs.y * zi1);
+      const cplx* cp = ccs[buf];
+      int t = 0;
+      while (t < cnt) {
+        if (rem == 0) {
+          if (s >= nsw) break;                 // inconsistent stream (flagged by k_ql): stop
+          if (s > 0) zp[1] = zc;               // flush the column carried by the previous sweep
+          const unsigned w = wnext;
+          ++s;
+          wnext = (s < nsw) ? sw[s] : 0u;
+          rem = (int)(w >> 8);
+          zp = zr + (w & 255u);
+          zc = zp[1];
+        }
+        int run = min(rem, cnt - t);
+        rem -= run;
+#pragma unroll 4
+        for (; run > 0; --run, ++t, --zp) {
+          const cplx cs = cp[t];
+          const double zi = zp[0];
+          zp[1] = fma(cs.y, zi, cs.x * zc);
+          zc = fma(-cs.y, zc, cs.x * zi);
+        }
       }
     }
+#pragma unroll
+    for (int q = 0; q < PRE; ++q) {
+      const int idx = tid + q * ROWS;
+      if (idx < APPLY_CHUNK && nb + idx < nr) ccs[buf ^ 1][idx] = pre[q];
+    }
+    __syncthreads();
   }
+  if (tid < rows && s > 0) zp[1] = zc;
   __syncthreads();
   for (int idx = tid; idx < rows * ff; idx += ROWS) {
     int rr = idx / ff, cc = idx - rr * ff;
     Wg[idx] = Z[rr * ld + cc];
   }
+  trc.done(P.trace, 3, b);
 }
 
 // ===================================================================================================

@@ -22,6 +22,8 @@ struct TileCfg {
   static constexpr int N = (FF - 1) / 2;
   static constexpr int NTHR = TR * TC;
   static constexpr int NT = ((NTHR + 31) / 32) * 32;
+  // register cap: MINB CTAs per SM must leave 4096 registers free for a co-resident k_ql warp of the sub-chunk pipeline
+  static constexpr int MAXREG = (((65536 - 4096) / (MINB * NT)) / 8) * 8;
   static constexpr int LD = (FF % 2) ? FF : FF + 1;   // odd leading dimension: conflict-free column walks
   static constexpr int KA_PER_KB = TR / TC;           // tile-row block index = kb / KA_PER_KB
   static_assert(TR * RT == FF && TC * CT == FF, "exact tiling only");
@@ -58,7 +60,7 @@ struct FrontSmem {
   } while (0)
 
 template <class C>
-__global__ void __launch_bounds__(C::NT, C::MINB) rk_front(KParams P) {
+__global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
   constexpr int FF = C::FF, TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, N = C::N, LD = C::LD, NT = C::NT;
   constexpr int z = 2 * N;
   using S = FrontSmem<C>;
@@ -85,6 +87,7 @@ __global__ void __launch_bounds__(C::NT, C::MINB) rk_front(KParams P) {
   const int ti = act ? tid / TC : TR - 1;
   const int tj = act ? tid % TC : TC - 1;
   __shared__ int sbad;
+  const CtaTrace trc(P.trace);
 
   for (int t = tid; t < nc; t += NT) twS[t] = P.tw[t];
 
@@ -494,6 +497,7 @@ __global__ void __launch_bounds__(C::NT, C::MINB) rk_front(KParams P) {
     if (tid == 0) P.wstatus[sidx] = sbad ? PIRL_ST_NPD : 0;
     RK_PHASE(7);
   }
+  trc.done(P.trace, 5, P.B);
 }
 
 // ===================================================================================================================
@@ -544,7 +548,7 @@ struct TailSmem {
 };
 
 template <class C, int MMAX>
-__global__ void __launch_bounds__(C::NT, 1) rk_tail(KParams P) {
+__global__ void __maxnreg__(C::MAXREG) rk_tail(KParams P) {
   constexpr int FF = C::FF, TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, N = C::N, LD = C::LD, NT = C::NT;
   constexpr int z = 2 * N;
   using S = TailSmem<C, MMAX>;
@@ -581,6 +585,7 @@ __global__ void __launch_bounds__(C::NT, 1) rk_tail(KParams P) {
   const bool act = tid < C::NTHR;
   const int ti = act ? tid / TC : TR - 1;
   const int tj = act ? tid % TC : TC - 1;
+  const CtaTrace trc(P.trace);
 
   for (int sidx = blockIdx.x; sidx < P.B; sidx += gridDim.x) {
     __syncthreads();
@@ -1014,4 +1019,5 @@ __global__ void __launch_bounds__(C::NT, 1) rk_tail(KParams P) {
     }
     RK_PHASE(14);
   }
+  trc.done(P.trace, 6, P.B);
 }
