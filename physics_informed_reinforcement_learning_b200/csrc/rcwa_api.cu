@@ -3,6 +3,7 @@
 // in the exported signatures.
 #include "rcwa_kernels.cuh"
 #include "rcwa_regtile.cuh"
+#include "rcwa_tail2.cuh"
 #include "../../include/pirl_rcwa.h"
 
 #include <complex>
@@ -56,7 +57,7 @@ struct pirl_handle {
   size_t ql_smem;
   unsigned long long* phase_clk = nullptr;   // [32] device counters (PIRL_PHASE_CLOCKS=1)
   unsigned long long* trace = nullptr;       // CTA trace records (PIRL_TRACE=1)
-  bool no_rktail = false;
+  bool no_rktail = false, old_rktail = false; int rk_tail2_grid = 0; size_t rk_tail2_smem = 0;
   bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
@@ -76,6 +77,9 @@ static constexpr int kNumStages = 7;
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
 using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2>;
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
+using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real tile at a time, two CTAs per SM
+#define RK_TAIL2 rk_tail2<Cfg81T2, 56, 10, 5>
+using Tail2Sm = Tail2Smem<Cfg81T2, 56, 10, 5>;
 static constexpr int kTailMmax = 64;   // 64 keeps rk_tail + one k_ql CTA within one SM's shared memory
 
 static cudaEvent_t take_event(pirl_handle* h) {
@@ -234,6 +238,13 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_tail<Cfg81T, kTailMmax>, Cfg81T::NT, h->rk_tail_smem));
     if (per_sm < 1) return fail(-9, "rk_tail does not fit on this device");
     h->rk_tail_grid = h->sm_count * per_sm;
+    h->rk_tail2_smem = (size_t)Tail2Sm::doubles * 8;
+    CUDA_TRY(cudaFuncSetAttribute(RK_TAIL2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    CUDA_TRY(max_carveout(RK_TAIL2));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, RK_TAIL2, Cfg81T2::NT, h->rk_tail2_smem));
+    if (per_sm < 1) return fail(-9, "rk_tail2 does not fit on this device");
+    h->rk_tail2_grid = h->sm_count * per_sm;
+    h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
   CUDA_TRY(max_carveout(k_apply<96>)); CUDA_TRY(max_carveout(k_apply<64>)); CUDA_TRY(max_carveout(k_apply<32>));
@@ -337,7 +348,8 @@ static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
   }
   if (h->regtile && !h->no_rktail) {
     StageTimer t(h, 6, st);
-    rk_tail<Cfg81T, kTailMmax><<<std::min(P.B, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
+    if (h->old_rktail) rk_tail<Cfg81T, kTailMmax><<<std::min(P.B, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
+    else RK_TAIL2<<<std::min(P.B, h->rk_tail2_grid), Cfg81T2::NT, h->rk_tail2_smem, st>>>(P);
     P.fallback_only = 1;
     h->launches += 1;
   }
