@@ -419,79 +419,127 @@ __global__ void __launch_bounds__(NT) k_tridiag(KParams P) {
 //   (first column hi, rotation count): a sweep rotates columns (hi, hi+1), (hi-1, hi), ... in that order.
 // ===================================================================================================
 __global__ void __launch_bounds__(32) k_ql(KParams P) {
+  // Lock-step organisation: the 32 lanes (32 structures) run one QL SWEEP per pass of the outer loop, the rotation loop
+  // has a warp-uniform trip count (longest sweep of the pass), and the search for negligible off-diagonals is folded into
+  // the sweep (every new e[k] is tested against its final neighbours as it is produced).  A lane never waits for another
+  // lane's extra iteration on the same eigenvalue, and the dependent chain of one rotation is rsqrt + 6 DFMA/DMUL.
+  // The rotation sequence is exactly the one of the textbook loop nest (for l: repeat {scan, shift, sweep}).
   extern __shared__ __align__(16) double sm[];
   const int ff = P.ff, lane = threadIdx.x;
   const int b = blockIdx.x * 32 + lane;
   const CtaTrace trc(P.trace);
-  if (b >= P.B) return;
+  const bool valid = b < P.B;
+  const int bb_ = valid ? b : P.B - 1;      // out-of-range lanes shadow the last structure (no stores)
   double* d = sm + lane;              // d[i] at d[i*32]
   double* e = sm + (size_t)ff * 32 + lane;
-  const double* tg = P.tri + (size_t)b * 2 * ff;
+  const double* tg = P.tri + (size_t)bb_ * 2 * ff;
   for (int i = 0; i < ff; ++i) { d[i * 32] = tg[i]; e[i * 32] = tg[ff + i]; }
   e[(ff - 1) * 32] = 0.0;
-  cplx* rc = P.rot_cs + (size_t)b * P.maxrot;
-  uint16_t* sw = P.sweeps + (size_t)b * P.maxsw;
+  cplx* rc = P.rot_cs + (size_t)bb_ * P.maxrot;
+  uint16_t* sw = P.sweeps + (size_t)bb_ * P.maxsw;
   int nrot = 0, nsw = 0;
   bool ok = true;
   const double eps = 2.220446049250313e-16;
-  for (int l = 0; l < ff; ++l) {
-    int it = 0;
-    while (true) {
-      int m = l;
-      while (m < ff - 1) {
-        double dsum = fabs(d[m * 32]) + fabs(d[(m + 1) * 32]);
-        if (fabs(e[m * 32]) <= eps * dsum) break;
-        ++m;
+  constexpr int NONE = 1 << 20;
+  int l = 0, it = 0, m = 0;
+  bool need_scan = true;
+  while (true) {
+    bool active = ok && l < ff - 1;
+    if (active && need_scan) {
+      while (true) {       // first negligible off-diagonal at or after l; converged eigenvalues are stepped over
+        m = l;
+        while (m < ff - 1) {
+          const double dsum = fabs(d[m * 32]) + fabs(d[(m + 1) * 32]);
+          if (fabs(e[m * 32]) <= eps * dsum) break;
+          ++m;
+        }
+        if (m != l) break;
+        ++l; it = 0;
+        if (l >= ff - 1) break;
       }
-      if (m == l) break;
-      if (++it > 60) { ok = false; break; }
+      need_scan = false;
+      active = l < ff - 1;
+    }
+    if (active && ++it > 60) { ok = false; active = false; }
+    if (!__any_sync(0xffffffffu, active)) break;
+    const int len = active ? m - l : 0;
+    const int maxlen = __reduce_max_sync(0xffffffffu, len);
+    double g = 0.0, s = 1.0, c = 1.0, p = 0.0;
+    if (active) {
       const double dl = d[l * 32], el = e[l * 32];
-      double g = (d[(l + 1) * 32] - dl) / (2.0 * el);
-      double r = sqrt(fma(g, g, 1.0));
+      g = (d[(l + 1) * 32] - dl) / (2.0 * el);
+      const double r = sqrt(fma(g, g, 1.0));
       g = d[m * 32] - dl + el / (g + copysign(r, g));
-      double s = 1.0, c = 1.0, p = 0.0;
-      int i = m - 1;
-      const int hi = i;
-      int cnt = 0;
-      bool underflow = false;
-      for (; i >= l; --i) {
-        const double ei = e[i * 32];
+    }
+    int i = m - 1;
+    const int hi = i;
+    int cnt = 0, first = NONE, second = NONE;
+    bool underflow = false;
+    double dold = active ? d[m * 32] : 0.0;                 // old d[i+1]
+    double ei = active ? e[i * 32] : 0.0;                   // old e[i]
+    double di = active ? d[i * 32] : 0.0;                   // old d[i]
+    double dn1 = 0.0;                                       // new d[i+2]
+    for (int step = 0; step < maxlen; ++step) {
+      if (step < len && !underflow) {
+        // prefetch the next step's operands (independent of the rotation chain)
+        const int in = (i > l) ? i - 1 : i;
+        const double ein = e[in * 32], din = d[in * 32];
         const double f = s * ei, bb = c * ei;
         const double h = fma(f, f, g * g);
         if (h == 0.0) {
           e[(i + 1) * 32] = 0.0;
-          d[(i + 1) * 32] -= p;
+          d[(i + 1) * 32] = dold - p;
           e[m * 32] = 0.0;
           underflow = true;
-          break;
+        } else {
+          const double rinv = rsqrt(h);      // one reciprocal square root instead of sqrt + divide on the critical path
+          const double enew = h * rinv;
+          e[(i + 1) * 32] = enew;
+          s = f * rinv;
+          c = g * rinv;
+          g = dold - p;
+          const double r = fma(di - g, s, 2.0 * c * bb);
+          p = s * r;
+          const double dn0 = g + p;
+          d[(i + 1) * 32] = dn0;
+          g = fma(c, r, -bb);
+          if (nrot < P.maxrot && valid) rc[nrot] = make_double2(c, s);
+          ++nrot; ++cnt;
+          if (step > 0 && enew <= eps * (fabs(dn0) + fabs(dn1))) { second = first; first = i + 1; }
+          dn1 = dn0;
+          dold = di; ei = ein; di = din;
+          --i;
         }
-        const double rinv = rsqrt(h);      // one reciprocal square root instead of sqrt + divide on the critical path
-        e[(i + 1) * 32] = h * rinv;
-        s = f * rinv;
-        c = g * rinv;
-        g = d[(i + 1) * 32] - p;
-        r = fma(d[i * 32] - g, s, 2.0 * c * bb);
-        p = s * r;
-        d[(i + 1) * 32] = g + p;
-        g = fma(c, r, -bb);
-        if (nrot < P.maxrot) rc[nrot] = make_double2(c, s);
-        ++nrot; ++cnt;
       }
-      if (cnt) { if (nsw < P.maxsw) sw[nsw] = (uint16_t)(hi | (cnt << 8)); ++nsw; }
-      if (underflow) continue;
-      d[l * 32] -= p;
-      e[l * 32] = g;
-      e[m * 32] = 0.0;
     }
-    if (!ok) break;
+    if (active) {
+      if (cnt) { if (nsw < P.maxsw && valid) sw[nsw] = (uint16_t)(hi | (cnt << 8)); ++nsw; }
+      if (underflow) { need_scan = true; }
+      else {
+        const double dln = dold - p;          // dold is the old d[l] after the last step
+        d[l * 32] = dln;
+        e[l * 32] = g;
+        e[m * 32] = 0.0;
+        if (fabs(g) <= eps * (fabs(dln) + fabs(dn1))) { second = first; first = l; }
+        const int mnew = first < m ? first : m;
+        if (mnew > l) m = mnew;
+        else {                                // eigenvalue l has converged
+          ++l; it = 0;
+          if (second != NONE) { if (second > l) m = second; else need_scan = true; }
+          else if (m <= l) need_scan = true;
+        }
+      }
+    }
   }
   if (nrot > P.maxrot) { ok = false; nrot = P.maxrot; }
   if (nsw > P.maxsw) { ok = false; nsw = 0; nrot = 0; }
-  double* lg = P.lam + (size_t)b * ff;
-  for (int i = 0; i < ff; ++i) lg[i] = d[i * 32];
-  P.nrot[b] = nrot;
-  P.nsw[b] = nsw;
-  if (!ok) atomicOr(&P.wstatus[b], PIRL_ST_EIG);
+  if (valid) {
+    double* lg = P.lam + (size_t)b * ff;
+    for (int i = 0; i < ff; ++i) lg[i] = d[i * 32];
+    P.nrot[b] = nrot;
+    P.nsw[b] = nsw;
+    if (!ok) atomicOr(&P.wstatus[b], PIRL_ST_EIG);
+  }
   __syncwarp();
   trc.done(P.trace, 2, b);
 }
