@@ -53,7 +53,7 @@ struct pirl_handle {
   int front_grid, front_mats; size_t front_smem;
   int tri_grid, tri_mats; size_t tri_smem;
   int tail_grid, tail_mats; size_t tail_smem;
-  int apply_rows; size_t apply_smem;
+  int apply_rows, apply_k; size_t apply_smem;
   size_t ql_smem;
   unsigned long long* phase_clk = nullptr;   // [32] device counters (PIRL_PHASE_CLOCKS=1)
   unsigned long long* trace = nullptr;       // CTA trace records (PIRL_TRACE=1)
@@ -75,7 +75,11 @@ static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "
 static constexpr int kNumStages = 7;
 
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
+#ifdef PIRL_FRONT_9x9
+using Cfg81 = TileCfg<81, 9, 9, 9, 9, 3>;
+#else
 using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2>;
+#endif
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
 using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real tile at a time, two CTAs per SM
 #define RK_TAIL2 rk_tail2<Cfg81T2, 56, 10, 5>
@@ -215,13 +219,15 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     else CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
   {
+    // k_apply: thread per row; K sweeps per systolic pass (4 for the headline size, 2 for the larger orders)
     h->apply_rows = (ff <= 96) ? 96 : 64;
-    const size_t apply_budget = budget - 2 * APPLY_CHUNK * sizeof(cplx);   // static rotation buffers of k_apply
-    h->apply_smem = (size_t)std::min(h->apply_rows, ff) * h->ld * 8;
-    if (h->apply_smem > apply_budget) { h->apply_rows = 32; h->apply_smem = 32 * (size_t)h->ld * 8; }
-    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_budget));
-    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_budget));
-    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_budget));
+    h->apply_k = (ff <= 96) ? 4 : 2;
+    auto apply_bytes = [&](int rows, int k) { return (size_t)(4 * apply_slots(ff, k) + (size_t)std::min(rows, ff) * apply_ld(ff, k)) * 8; };
+    h->apply_smem = apply_bytes(h->apply_rows, h->apply_k);
+    if (h->apply_smem > budget) { h->apply_rows = 32; h->apply_smem = apply_bytes(32, h->apply_k); }
+    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
@@ -247,7 +253,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
-  CUDA_TRY(max_carveout(k_apply<96>)); CUDA_TRY(max_carveout(k_apply<64>)); CUDA_TRY(max_carveout(k_apply<32>));
+  CUDA_TRY(max_carveout(k_apply<96, 4>)); CUDA_TRY(max_carveout(k_apply<64, 2>)); CUDA_TRY(max_carveout(k_apply<32, 2>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
   CUDA_TRY(max_carveout(rk_front<Cfg81>)); CUDA_TRY(max_carveout(rk_tail<Cfg81T, kTailMmax>));
   if (getenv("PIRL_TRACE")) {
@@ -341,9 +347,9 @@ static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
   {
     StageTimer t(h, 3, st);
     dim3 g(P.B, (h->ff + h->apply_rows - 1) / h->apply_rows);
-    if (h->apply_rows == 96) k_apply<96><<<g, 96, h->apply_smem, st>>>(P);
-    else if (h->apply_rows == 64) k_apply<64><<<g, 64, h->apply_smem, st>>>(P);
-    else k_apply<32><<<g, 32, h->apply_smem, st>>>(P);
+    if (h->apply_rows == 96) k_apply<96, 4><<<g, 96, h->apply_smem, st>>>(P);
+    else if (h->apply_rows == 64) k_apply<64, 2><<<g, 64, h->apply_smem, st>>>(P);
+    else k_apply<32, 2><<<g, 32, h->apply_smem, st>>>(P);
     h->launches += 1;
   }
   if (h->regtile && !h->no_rktail) {

@@ -545,84 +545,123 @@ __global__ void __launch_bounds__(32) k_ql(KParams P) {
 }
 
 // ===================================================================================================
-// k_apply : W = M0 * G_1 * G_2 * ...   Each thread owns one row of the basis in shared memory.  Within a QL sweep
-//   consecutive rotations share a column, so the shared value is carried in a register: one shared load, one shared
-//   store and a single dependent DFMA per rotation.  Rotations are staged through a double-buffered static shared
-//   array (distinct object from the rows: the compiler may hoist the loads of an unrolled group).
+// k_apply : W = M0 * G_1 * G_2 * ...   Each thread owns one row of the basis in shared memory.
+//   K consecutive QL sweeps are applied together as a systolic pipeline: stage j works two columns behind stage j-1, the
+//   values between the stages stay in registers, so one step (K rotations) costs one shared load and one shared store of
+//   the row element instead of K of each (the single-sweep version was bound by shared-memory wavefronts).
+//   At step i stage j rotates columns (i + 2j, i + 2j + 1); where a sweep does not cover that column the stage gets the
+//   identity rotation.  The rotations of a group are staged into shared memory in step-major order ([step][stage]) while
+//   the previous group is being applied (double buffer).  Rows carry 2K-1 padding columns on both sides so that the hot
+//   loop needs no bounds checks.
 // ===================================================================================================
-#define APPLY_CHUNK 256
-template <int ROWS>
+template <int K>
+__host__ __device__ constexpr int apply_pad() { return 2 * K - 1; }
+__host__ __device__ inline int apply_ld(int ff, int K) { int ld = ff + 2 * (2 * K - 1); return ld | 1; }
+__host__ __device__ inline int apply_slots(int ff, int K) { return (ff + 2 * K) * K; }
+
+template <int ROWS, int K>
 __global__ void __launch_bounds__(ROWS) k_apply(KParams P) {
-  extern __shared__ __align__(16) double Z[];
-  __shared__ cplx ccs[2][APPLY_CHUNK];
-  const int ff = P.ff, ld = P.ld, tid = threadIdx.x;
+  extern __shared__ __align__(16) double smem_apply[];
+  const int ff = P.ff, tid = threadIdx.x;
+  const int ld = apply_ld(ff, K), nslots = apply_slots(ff, K);
+  constexpr int PAD = apply_pad<K>();
+  cplx* rbuf = reinterpret_cast<cplx*>(smem_apply);          // [2][nslots]
+  double* Z = smem_apply + 4 * (size_t)nslots;               // [rows][ld]
   const int b = blockIdx.x, r0 = blockIdx.y * ROWS;
   const int rows = min(ROWS, ff - r0);
   const CtaTrace trc(P.trace);
   double* Wg = P.Wbuf + (size_t)b * ff * ff + (size_t)r0 * ff;
+  for (int idx = tid; idx < rows * ld; idx += ROWS) Z[idx] = 0.0;
+  __syncthreads();
   for (int idx = tid; idx < rows * ff; idx += ROWS) {
     int rr = idx / ff, cc = idx - rr * ff;
-    Z[rr * ld + cc] = Wg[idx];
+    Z[rr * ld + PAD + cc] = Wg[idx];
   }
   const int nr = min(P.nrot[b], P.maxrot);
   const int nsw = min(P.nsw[b], P.maxsw);
   const cplx* rc = P.rot_cs + (size_t)b * P.maxrot;
   const uint16_t* sw = P.sweeps + (size_t)b * P.maxsw;
-  for (int t = tid; t < min(APPLY_CHUNK, nr); t += ROWS) ccs[0][t] = rc[t];
-  __syncthreads();
-  constexpr int PRE = (APPLY_CHUNK + ROWS - 1) / ROWS;
-  double* zr = Z + (tid < rows ? tid : 0) * ld;
-  double* zp = zr;
-  double zc = 0.0;
-  int s = 0, rem = 0;
-  unsigned wnext = (nsw > 0) ? sw[0] : 0u;
-  int buf = 0;
-  for (int base = 0; base < nr; base += APPLY_CHUNK, buf ^= 1) {
-    const int cnt = min(APPLY_CHUNK, nr - base);
-    const int nb = base + APPLY_CHUNK;
-    cplx pre[PRE];
+  double* zr = Z + (tid < rows ? tid : 0) * ld + PAD;
+  constexpr int PRE = 4;                                      // slots per thread prefetched under the previous group
+  // group descriptors (uniform): hi, lo, base of the K sweeps; step range of the group
+  int ghi[K], glo[K], gbase[K];
+  int istart = 0, iend = 0, base_next = 0;
+  auto load_group = [&](int g) {
+    istart = -(1 << 20); iend = 1 << 20;
 #pragma unroll
-    for (int q = 0; q < PRE; ++q) {
-      const int idx = tid + q * ROWS;
-      if (idx < APPLY_CHUNK && nb + idx < nr) pre[q] = rc[nb + idx];
+    for (int j = 0; j < K; ++j) {
+      const int sidx = g * K + j;
+      unsigned w = (sidx < nsw) ? sw[sidx] : 0u;
+      int cnt = (int)(w >> 8);
+      const int hi = (int)(w & 255u);
+      if (base_next + cnt > nr) cnt = max(nr - base_next, 0);     // inconsistent stream (flagged by k_ql)
+      ghi[j] = hi; glo[j] = hi - cnt + 1; gbase[j] = base_next;
+      base_next += cnt;
+      if (cnt > 0) { istart = max(istart, hi - 2 * j); iend = min(iend, hi - cnt + 1 - 2 * j); }
     }
-    if (tid < rows) {
-      const cplx* cp = ccs[buf];
-      int t = 0;
-      while (t < cnt) {
-        if (rem == 0) {
-          if (s >= nsw) break;                 // inconsistent stream (flagged by k_ql): stop
-          if (s > 0) zp[1] = zc;               // flush the column carried by the previous sweep
-          const unsigned w = wnext;
-          ++s;
-          wnext = (s < nsw) ? sw[s] : 0u;
-          rem = (int)(w >> 8);
-          zp = zr + (w & 255u);
-          zc = zp[1];
-        }
-        int run = min(rem, cnt - t);
-        rem -= run;
-#pragma unroll 4
-        for (; run > 0; --run, ++t, --zp) {
-          const cplx cs = cp[t];
-          const double zi = zp[0];
-          zp[1] = fma(cs.y, zi, cs.x * zc);
-          zc = fma(-cs.y, zc, cs.x * zi);
+    if (iend > istart) { istart = 0; iend = 1; }              // empty group: zero steps
+  };
+  // staging of the group in (ghi, glo, gbase, istart, iend): slot [t*K + j] = rotation of stage j at step t (or identity)
+  auto fetch_slot = [&](int idx, int T) -> cplx {
+    cplx v = make_double2(1.0, 0.0);
+    if (idx < T * K) {
+      const int t = idx / K, j = idx - t * K;
+      int hi = ghi[0], lo = glo[0], bs = gbase[0];
+#pragma unroll
+      for (int jj = 1; jj < K; ++jj) if (j == jj) { hi = ghi[jj]; lo = glo[jj]; bs = gbase[jj]; }
+      const int c = istart - t + 2 * j;
+      if (c <= hi && c >= lo) v = rc[bs + (hi - c)];
+    }
+    return v;
+  };
+  cplx pre[PRE];
+  auto stage_issue = [&]() {                                  // global loads of the first PRE*ROWS slots into registers
+    const int T = istart - iend + 1;
+#pragma unroll
+    for (int q = 0; q < PRE; ++q) pre[q] = fetch_slot(tid + q * ROWS, T);
+  };
+  auto stage_commit = [&](cplx* dst) {                        // registers -> shared; remaining slots directly
+    const int T = istart - iend + 1;
+#pragma unroll
+    for (int q = 0; q < PRE; ++q) { const int idx = tid + q * ROWS; if (idx < T * K) dst[idx] = pre[q]; }
+    for (int idx = PRE * ROWS + tid; idx < T * K; idx += ROWS) dst[idx] = fetch_slot(idx, T);
+  };
+  const int ngroups = (nsw + K - 1) / K;
+  if (ngroups > 0) { load_group(0); stage_issue(); stage_commit(rbuf); }
+  __syncthreads();
+  for (int g = 0; g < ngroups; ++g) {
+    const cplx* cp = rbuf + (size_t)(g & 1) * nslots;
+    const int is = istart, T = istart - iend + 1;
+    // descriptors and staging of the next group (global loads in flight while this group is applied)
+    if (g + 1 < ngroups) { load_group(g + 1); stage_issue(); }
+    if (tid < rows && T > 0) {
+      double carry[K], dl[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) { carry[j] = zr[is + 2 * j + 1]; dl[j] = zr[is + 2 * j + 2]; }
+      double* zp = zr + is;
+#pragma unroll 2
+      for (int t = 0; t < T; ++t, --zp, cp += K) {
+        const double in0 = zp[0];
+        // last stage first: it consumes the value the previous stage produced one step ago
+#pragma unroll
+        for (int j = K - 1; j >= 0; --j) {
+          const cplx cs = cp[j];
+          const double in = (j == 0) ? in0 : dl[j - 1];
+          const double out = fma(cs.y, in, cs.x * carry[j]);
+          carry[j] = fma(-cs.y, carry[j], cs.x * in);
+          if (j == K - 1) zp[2 * K - 1] = out; else dl[j] = out;
         }
       }
-    }
+      // flush: zp now points at column (i_end - 1)
 #pragma unroll
-    for (int q = 0; q < PRE; ++q) {
-      const int idx = tid + q * ROWS;
-      if (idx < APPLY_CHUNK && nb + idx < nr) ccs[buf ^ 1][idx] = pre[q];
+      for (int j = 0; j < K; ++j) { zp[2 * j + 1] = carry[j]; if (j < K - 1) zp[2 * j + 2] = dl[j]; }
     }
+    if (g + 1 < ngroups) stage_commit(rbuf + (size_t)((g + 1) & 1) * nslots);
     __syncthreads();
   }
-  if (tid < rows && s > 0) zp[1] = zc;
-  __syncthreads();
   for (int idx = tid; idx < rows * ff; idx += ROWS) {
     int rr = idx / ff, cc = idx - rr * ff;
-    Wg[idx] = Z[rr * ld + cc];
+    Wg[idx] = Z[rr * ld + PAD + cc];
   }
   trc.done(P.trace, 3, b);
 }
