@@ -222,12 +222,13 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     // k_apply: thread per row; K sweeps per systolic pass (4 for the headline size, 2 for the larger orders)
     h->apply_rows = (ff <= 96) ? 96 : 64;
     h->apply_k = (ff <= 96) ? 4 : 2;
-    auto apply_bytes = [&](int rows, int k) { return (size_t)(4 * apply_slots(ff, k) + (size_t)std::min(rows, ff) * apply_ld(ff, k)) * 8; };
+    auto apply_bytes = [&](int rows, int k) { return (size_t)std::min(rows, ff) * apply_ld(ff, k) * 8; };
+    const size_t abudget = budget - 2 * (size_t)(256 + 2 * 4) * 4 * sizeof(cplx);   // static rotation buffers
     h->apply_smem = apply_bytes(h->apply_rows, h->apply_k);
-    if (h->apply_smem > budget) { h->apply_rows = 32; h->apply_smem = apply_bytes(32, h->apply_k); }
-    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
-    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
-    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    if (h->apply_smem > abudget) { h->apply_rows = 32; h->apply_smem = apply_bytes(32, h->apply_k); }
+    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4, 81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
+    else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
+    else CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
@@ -253,7 +254,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
-  CUDA_TRY(max_carveout(k_apply<96, 4>)); CUDA_TRY(max_carveout(k_apply<64, 2>)); CUDA_TRY(max_carveout(k_apply<32, 2>));
+  CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
   CUDA_TRY(max_carveout(rk_front<Cfg81>)); CUDA_TRY(max_carveout(rk_tail<Cfg81T, kTailMmax>));
   if (getenv("PIRL_TRACE")) {
@@ -347,9 +348,9 @@ static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
   {
     StageTimer t(h, 3, st);
     dim3 g(P.B, (h->ff + h->apply_rows - 1) / h->apply_rows);
-    if (h->apply_rows == 96) k_apply<96, 4><<<g, 96, h->apply_smem, st>>>(P);
-    else if (h->apply_rows == 64) k_apply<64, 2><<<g, 64, h->apply_smem, st>>>(P);
-    else k_apply<32, 2><<<g, 32, h->apply_smem, st>>>(P);
+    if (h->apply_rows == 96) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
+    else if (h->apply_rows == 64) k_apply<64, 2, 256><<<g, 64, h->apply_smem, st>>>(P);
+    else k_apply<32, 2, 256><<<g, 32, h->apply_smem, st>>>(P);
     h->launches += 1;
   }
   if (h->regtile && !h->no_rktail) {

@@ -559,14 +559,17 @@ __host__ __device__ constexpr int apply_pad() { return 2 * K - 1; }
 __host__ __device__ inline int apply_ld(int ff, int K) { int ld = ff + 2 * (2 * K - 1); return ld | 1; }
 __host__ __device__ inline int apply_slots(int ff, int K) { return (ff + 2 * K) * K; }
 
-template <int ROWS, int K>
+template <int ROWS, int K, int FFMAX>
 __global__ void __launch_bounds__(ROWS) k_apply(KParams P) {
-  extern __shared__ __align__(16) double smem_apply[];
+  extern __shared__ __align__(16) double Z[];                // [rows][ld]
+  // the rotation buffers are a separate (static) object: the compiler may then hoist their loads over the row stores
+  constexpr int nslots = (FFMAX + 2 * K) * K;
+  __shared__ cplx rbuf[2 * nslots];
+  constexpr int SWS = 256;                                    // sweep descriptors kept in shared memory (rest: global)
+  __shared__ uint16_t ssw[SWS];
   const int ff = P.ff, tid = threadIdx.x;
-  const int ld = apply_ld(ff, K), nslots = apply_slots(ff, K);
+  const int ld = apply_ld(ff, K);
   constexpr int PAD = apply_pad<K>();
-  cplx* rbuf = reinterpret_cast<cplx*>(smem_apply);          // [2][nslots]
-  double* Z = smem_apply + 4 * (size_t)nslots;               // [rows][ld]
   const int b = blockIdx.x, r0 = blockIdx.y * ROWS;
   const int rows = min(ROWS, ff - r0);
   const CtaTrace trc(P.trace);
@@ -581,6 +584,8 @@ __global__ void __launch_bounds__(ROWS) k_apply(KParams P) {
   const int nsw = min(P.nsw[b], P.maxsw);
   const cplx* rc = P.rot_cs + (size_t)b * P.maxrot;
   const uint16_t* sw = P.sweeps + (size_t)b * P.maxsw;
+  for (int t = tid; t < min(nsw, SWS); t += ROWS) ssw[t] = sw[t];
+  __syncthreads();
   double* zr = Z + (tid < rows ? tid : 0) * ld + PAD;
   constexpr int PRE = 4;                                      // slots per thread prefetched under the previous group
   // group descriptors (uniform): hi, lo, base of the K sweeps; step range of the group
@@ -591,7 +596,7 @@ __global__ void __launch_bounds__(ROWS) k_apply(KParams P) {
 #pragma unroll
     for (int j = 0; j < K; ++j) {
       const int sidx = g * K + j;
-      unsigned w = (sidx < nsw) ? sw[sidx] : 0u;
+      unsigned w = (sidx < nsw) ? (sidx < SWS ? ssw[sidx] : sw[sidx]) : 0u;
       int cnt = (int)(w >> 8);
       const int hi = (int)(w & 255u);
       if (base_next + cnt > nr) cnt = max(nr - base_next, 0);     // inconsistent stream (flagged by k_ql)
