@@ -644,18 +644,28 @@ __global__ void __launch_bounds__(ROWS) k_apply(KParams P) {
 #pragma unroll
       for (int j = 0; j < K; ++j) { carry[j] = zr[is + 2 * j + 1]; dl[j] = zr[is + 2 * j + 2]; }
       double* zp = zr + is;
+      // software pipeline: the rotations and the row element of step t+1 are loaded while step t is computed
+      cplx cs[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) cs[j] = cp[j];
+      double in0 = zp[0];
 #pragma unroll 2
       for (int t = 0; t < T; ++t, --zp, cp += K) {
-        const double in0 = zp[0];
+        cplx csn[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) csn[j] = cp[K + j];     // (one step past the group at the end: inside the buffer, unused)
+        const double in0n = zp[-1];
         // last stage first: it consumes the value the previous stage produced one step ago
 #pragma unroll
         for (int j = K - 1; j >= 0; --j) {
-          const cplx cs = cp[j];
           const double in = (j == 0) ? in0 : dl[j - 1];
-          const double out = fma(cs.y, in, cs.x * carry[j]);
-          carry[j] = fma(-cs.y, carry[j], cs.x * in);
+          const double out = fma(cs[j].y, in, cs[j].x * carry[j]);
+          carry[j] = fma(-cs[j].y, carry[j], cs[j].x * in);
           if (j == K - 1) zp[2 * K - 1] = out; else dl[j] = out;
         }
+#pragma unroll
+        for (int j = 0; j < K; ++j) cs[j] = csn[j];
+        in0 = in0n;
       }
       // flush: zp now points at column (i_end - 1)
 #pragma unroll
