@@ -239,6 +239,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     int per_sm = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_front<Cfg81>, Cfg81::NT, h->rk_front_smem));
     if (per_sm < 1) return fail(-9, "rk_front does not fit on this device");
+    if (const char* e = getenv("PIRL_FRONT_PER_SM")) per_sm = std::max(1, std::min(per_sm, atoi(e)));   // experiment knob
     h->rk_front_grid = h->sm_count * per_sm;
     h->rk_tail_smem = (size_t)TailSmem<Cfg81T, kTailMmax>::doubles * 8;
     CUDA_TRY(cudaFuncSetAttribute(rk_tail<Cfg81T, kTailMmax>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
@@ -250,6 +251,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     CUDA_TRY(max_carveout(RK_TAIL2));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, RK_TAIL2, Cfg81T2::NT, h->rk_tail2_smem));
     if (per_sm < 1) return fail(-9, "rk_tail2 does not fit on this device");
+    if (const char* e = getenv("PIRL_TAIL_PER_SM")) per_sm = std::max(1, std::min(per_sm, atoi(e)));   // experiment knob
     h->rk_tail2_grid = h->sm_count * per_sm;
     h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }

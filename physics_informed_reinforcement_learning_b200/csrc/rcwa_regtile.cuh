@@ -22,8 +22,8 @@ struct TileCfg {
   static constexpr int N = (FF - 1) / 2;
   static constexpr int NTHR = TR * TC;
   static constexpr int NT = ((NTHR + 31) / 32) * 32;
-  // register cap: MINB CTAs per SM must leave 4096 registers free for a co-resident k_ql warp of the sub-chunk pipeline
-  static constexpr int MAXREG = (((65536 - 4096) / (MINB * NT)) / 8) * 8;
+  // register cap for MINB CTAs per SM
+  static constexpr int MAXREG = ((65536 / (MINB * NT)) / 8) * 8;
   static constexpr int LD = (FF % 2) ? FF : FF + 1;   // odd leading dimension: conflict-free column walks
   static constexpr int KA_PER_KB = TR / TC;           // tile-row block index = kb / KA_PER_KB
   static_assert(TR * RT == FF && TC * CT == FF, "exact tiling only");

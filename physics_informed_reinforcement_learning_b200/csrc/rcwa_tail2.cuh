@@ -38,7 +38,7 @@ struct Tail2Smem {
   static constexpr int qP = beta + 2 * NHMAX;                 // [NPMAX] |q| of the propagating modes
   static constexpr int XP = qP + pirl_even(NPMAX);            // [NPMAX] complex
   static constexpr int cb = XP + 2 * NPMAX;                   // [2][FE] published pivot column
-  static constexpr int sc = cb + 2 * FE;                      // [2][NXB + 2] published row of the extra columns (+ spare)
+  static constexpr int sc = cb + 2 * FE;                      // [2][NXB + 2] published row of the extra columns, 1/pivot, pivot
   static constexpr int Yt = sc + 2 * (NXB + 2);               // [FF][NHMAX]
   static constexpr int dt = Yt + pirl_even(C::FF * NHMAX);    // [FE]
   static constexpr int CT = dt + FE;                          // [NCT][NCT]
@@ -79,10 +79,13 @@ __device__ __forceinline__ void t2_ldlt_range(double (&t)[C::RT][C::CT], double 
       const int kti = k - ka * TR;
       double* cb = cbuf + (k & 1) * FE;
       double* sc = scbuf + (k & 1) * SCW;
+      // publisher side does all the masking: finished rows (and the pivot itself) are published as zeros, the pivot
+      // owner also publishes 1/d, so the readers' inner step is loads + multiply-adds only
       if (act) {
         if (tj == kj) {
 #pragma unroll
-          for (int a = 0; a < RT; ++a) if (a >= ka) cb[ti + TR * a] = t[a][kb];
+          for (int a = 0; a < RT; ++a) if (a >= ka) { const int i = ti + TR * a; cb[i] = (i > k) ? t[a][kb] : 0.0; }
+          if (ti == kti) { const double d = t[ka][kb]; sc[SCW - 2] = 1.0 / d; sc[SCW - 1] = d; }
         }
         if (ti == kti) {
           sc[tj] = x0[ka];
@@ -90,15 +93,12 @@ __device__ __forceinline__ void t2_ldlt_range(double (&t)[C::RT][C::CT], double 
         }
       }
       __syncthreads();
-      const double d = cb[k];
-      if (!(d > 0.0)) bad = 1;
-      const double pinv = 1.0 / d;
+      const double pinv = sc[SCW - 2];
       if (tid < nx) Ys[k * NXS + tid] = sc[tid];
-      if (tid == 32) ds[k] = d;
+      if (tid == 32) ds[k] = sc[SCW - 1];
       double l[RT];
 #pragma unroll
-      for (int a = 0; a < RT; ++a)
-        if (a >= ka) { const int i = ti + TR * a; l[a] = (i > k) ? cb[i] * pinv : 0.0; }
+      for (int a = 0; a < RT; ++a) if (a >= ka) l[a] = cb[ti + TR * a] * pinv;
       const double y0 = sc[tj];
 #pragma unroll
       for (int a = 0; a < RT; ++a) if (a >= ka) x0[a] = fma(-l[a], y0, x0[a]);
@@ -110,8 +110,7 @@ __device__ __forceinline__ void t2_ldlt_range(double (&t)[C::RT][C::CT], double 
 #pragma unroll
       for (int b = 0; b < CT; ++b)
         if (b >= kb) {
-          const int j = tj + TC * b;
-          const double r = (j > k) ? cb[j] : 0.0;
+          const double r = cb[tj + TC * b];
 #pragma unroll
           for (int a = 0; a < RT; ++a) if (a >= ka) t[a][b] = fma(-l[a], r, t[a][b]);
         }
@@ -145,33 +144,31 @@ __device__ __forceinline__ void t2_sweep_range(double (&t)[C::RT][C::CT], double
       const int kti = k - ka * TR;
       double* cb = cbuf + (k & 1) * FE;
       double* sc = scbuf + (k & 1) * SCW;
+      // published column: zeros on finished rows, d - 1 at the pivot (so that u_k = -(d - 1) p = p - 1 and v_k = d - 1 need
+      // no special case on the reader side); the pivot owner also publishes 1/d
       if (act) {
         if (tj == kj) {
 #pragma unroll
-          for (int a = 0; a < RT; ++a) if (a >= a0) cb[ti + TR * a] = t[a][kb];
+          for (int a = 0; a < RT; ++a)
+            if (a >= a0) { const int i = ti + TR * a; cb[i] = (i >= kbeg) ? ((i == k) ? t[a][kb] - 1.0 : t[a][kb]) : 0.0; }
+          if (ti == kti) { const double d = t[ka][kb]; sc[SCW - 2] = 1.0 / d; sc[SCW - 1] = d; }
         }
         if (ti == kti) sc[tj] = x0[ka];
       }
       __syncthreads();
-      const double d = cb[k];
-      if (!(d > 0.0)) bad = 1;
-      const double p = 1.0 / d;
+      const double p = sc[SCW - 2];
       if (tid < nx) Ys[k * NXS + tid] = sc[tid];
-      if (tid == 32) ds[k] = d;
-      // rank-1 form of the sweep: t += u_i v_j with u_i = -c_i p (i != k), u_k = p - 1, v_j = c_j (j != k), v_k = d - 1;
-      // the (k, k) entry is fixed up afterwards (must become -p).
+      if (tid == 32) ds[k] = sc[SCW - 1];
       double u[RT];
 #pragma unroll
-      for (int a = 0; a < RT; ++a)
-        if (a >= a0) { const int i = ti + TR * a; u[a] = (i == k) ? (p - 1.0) : ((i >= kbeg) ? -cb[i] * p : 0.0); }
+      for (int a = 0; a < RT; ++a) if (a >= a0) u[a] = -cb[ti + TR * a] * p;
       const double y0 = sc[tj];
 #pragma unroll
       for (int a = 0; a < RT; ++a) if (a >= a0) x0[a] = fma(u[a], y0, x0[a]);
 #pragma unroll
       for (int b = 0; b < CT; ++b)
         if (b >= b0) {
-          const int j = tj + TC * b;
-          const double v = (j == k) ? (d - 1.0) : ((j >= kbeg) ? cb[j] : 0.0);
+          const double v = cb[tj + TC * b];
 #pragma unroll
           for (int a = 0; a < RT; ++a) if (a >= a0) t[a][b] = fma(u[a], v, t[a][b]);
         }
@@ -398,14 +395,15 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
       double s = 0.0;
       if (idx < nhI * nhI) {
         const int a = idx / nhI, b = idx - a * nhI;
-        for (int k = 0; k < ne; ++k) s = fma(Yt[k * NHMAX + a] / dt[k], Yt[k * NHMAX + b], s);
+        for (int k = 0; k < ne; ++k) { if (!(dt[k] > 0.0)) bad = 1; s = fma(Yt[k * NHMAX + a] / dt[k], Yt[k * NHMAX + b], s); }
         CTm[(np + a) * NCT + np + b] = -s;
       } else {
         const int q = idx - nhI * nhI, a = q / nxb, b = q - a * nxb;
-        for (int k = 0; k < ne; ++k) s = fma(Yb[k * NXB + a] / db[k], Yb[k * NXB + b], s);
+        for (int k = 0; k < ne; ++k) { if (!(db[k] > 0.0)) bad = 1; s = fma(Yb[k * NXB + a] / db[k], Yb[k * NXB + b], s); }
         CBm[(np + a) * NCB + np + b] = -s;
       }
     }
+    if (bad) cnt[5] = 1;       // a non-positive pivot: K was not positive definite
     __syncthreads();
     RK_PHASE(14);
     // =========================== border system [h_t,P | tau | hb_P | sigma | c_P] ===========================
@@ -533,7 +531,7 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
       det[1] = (T0.x * T0.x + T0.y * T0.y) * nI / nII;
       det[2] = (Tp.x * Tp.x + Tp.y * Tp.y) * k1II / (nII * nII) * nI;
       int st = P.wstatus[sidx];
-      if (bad || !isfinite(det[0]) || !isfinite(det[1]) || !isfinite(der[1])) st |= PIRL_ST_NONFINITE_;   // bad: a non-positive pivot (uniform)
+      if (cnt[5] || !isfinite(det[0]) || !isfinite(det[1]) || !isfinite(der[1])) st |= PIRL_ST_NONFINITE_;
       P.eff[sidx] = det[0];
       if (P.de_r3) { P.de_r3[3 * sidx] = der[0]; P.de_r3[3 * sidx + 1] = der[1]; P.de_r3[3 * sidx + 2] = der[2]; }
       if (P.de_t3) { P.de_t3[3 * sidx] = det[0]; P.de_t3[3 * sidx + 1] = det[1]; P.de_t3[3 * sidx + 2] = det[2]; }
