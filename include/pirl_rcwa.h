@@ -76,6 +76,18 @@ int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const double* params,
 int pirl_rcwa_eval_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
                         int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status);
 
+/* Batched efficiency + adjoint gradient d eff / d s_p (p = 0..n_cells-1), s_p the cell value of solver.py:21-22
+ * (u = (s+1)/2, eps = u (n_r^2 - n_g^2) + n_g^2, 1/eps taken cell by cell before convolution_matrix.py:89-114).
+ * The reference has no gradient code; the contract is the central finite difference of its forward solver
+ * (reproduce_acs_cell, solver.py:16-38) with respect to one continuous cell value.
+ *   eff   device, double [B]            grad   device, double [B][n_cells]
+ * Reverse-mode sweep through the same factorisations as pirl_rcwa_eval (about 3x the cost of a forward call). */
+int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                        int64_t B, double* eff, double* grad, int32_t* status, void* stream);
+/* Same with HOST buffers (H2D, eval + gradient, D2H, synchronous). */
+int pirl_rcwa_eval_grad_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                             int64_t B, double* eff, double* grad, int32_t* status);
+
 /* DeflectorBase.flip for B envs (base.py:37-42): patterns[b][a] = -patterns[b][a] iff 0 <= a <= n_cells-1. */
 int pirl_env_flip(int8_t* patterns, const int64_t* actions, int64_t B, int32_t n_cells, void* stream);
 

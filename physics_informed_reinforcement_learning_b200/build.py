@@ -9,7 +9,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libpirl_rcwa.so")
 SOURCES = ["rcwa_api.cu"]
-DEPENDS = ["rcwa_api.cu", "rcwa_kernels.cuh", "rcwa_regtile.cuh", "rcwa_tail2.cuh", os.path.join("..", "..", "include", "pirl_rcwa.h")]
+DEPENDS = ["rcwa_api.cu", "rcwa_kernels.cuh", "rcwa_regtile.cuh", "rcwa_tail2.cuh", "rcwa_grad.cuh", os.path.join("..", "..", "include", "pirl_rcwa.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

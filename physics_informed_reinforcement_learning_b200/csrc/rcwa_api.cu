@@ -4,6 +4,7 @@
 #include "rcwa_kernels.cuh"
 #include "rcwa_regtile.cuh"
 #include "rcwa_tail2.cuh"
+#include "rcwa_grad.cuh"
 #include "../../include/pirl_rcwa.h"
 
 #include <complex>
@@ -65,14 +66,19 @@ struct pirl_handle {
   int8_t* hd_patterns = nullptr; double* hd_params = nullptr; double* hd_out = nullptr; int32_t* hd_status = nullptr;
   int64_t hd_cap = 0;
   cudaStream_t own_stream = nullptr;
+  // adjoint gradient (allocated on the first pirl_rcwa_eval_grad)
+  double *g_lamb = nullptr, *g_Lf = nullptr, *g_Rf = nullptr, *g_scr_tail = nullptr, *g_scr_eig = nullptr;
+  int g_tail_grid = 0, g_tail_mats = 0, g_eig_grid = 0, g_eig_mats = 0;
+  size_t g_tail_smem = 0, g_eig_smem = 0, g_tail_stride = 0, g_eig_stride = 0;
+  double* hd_grad = nullptr; int64_t hd_grad_cap = 0;
   // per-kernel timing (pirl_rcwa_set_stage_timing)
   bool timing = false;
   std::vector<cudaEvent_t> ev_free;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
 };
 
-static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail"};
-static constexpr int kNumStages = 7;
+static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail", "g_tail", "g_eigback"};
+static constexpr int kNumStages = 9;
 
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
 #ifdef PIRL_FRONT_9x9
@@ -298,6 +304,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
   cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace);
   cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
+  cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
   for (auto e : h->evF) if (e) cudaEventDestroy(e);
@@ -346,15 +353,17 @@ static void launch_ql(pirl_handle* h, const KParams& P, cudaStream_t st) {
   h->launches += 1;
 }
 
-static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
-  {
+static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
     StageTimer t(h, 3, st);
     dim3 g(P.B, (h->ff + h->apply_rows - 1) / h->apply_rows);
     if (h->apply_rows == 96) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 64) k_apply<64, 2, 256><<<g, 64, h->apply_smem, st>>>(P);
     else k_apply<32, 2, 256><<<g, 32, h->apply_smem, st>>>(P);
     h->launches += 1;
-  }
+}
+
+static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
+  launch_apply(h, P, st);
   if (h->regtile && !h->no_rktail) {
     StageTimer t(h, 6, st);
     if (h->old_rktail) rk_tail<Cfg81T, kTailMmax><<<std::min(P.B, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
@@ -371,8 +380,8 @@ static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
   h->launches += 1;
 }
 
-static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
-                        double* eff, double* de_r3, double* de_t3, int32_t* status, cudaStream_t st) {
+static KParams chunk_params(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
+                            double* eff, double* de_r3, double* de_t3, int32_t* status) {
   KParams P;
   memset(&P, 0, sizeof(P));
   P.n_cells = h->cfg.n_cells; P.N = h->cfg.order; P.ff = h->ff; P.ld = h->ld; P.B = Bc;
@@ -383,6 +392,12 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   P.wstatus = h->wstatus; P.phase_clk = h->phase_clk; P.trace = h->trace;
   P.scratch = h->scratch; P.scratch_stride = h->scratch_stride;
   P.eff = eff; P.de_r3 = de_r3; P.de_t3 = de_t3; P.status = status;
+  return P;
+}
+
+static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
+                        double* eff, double* de_r3, double* de_t3, int32_t* status, cudaStream_t st) {
+  KParams P = chunk_params(h, patterns, params, pstride, Bc, eff, de_r3, de_t3, status);
 
   // Sub-chunk pipeline.  k_ql is one thread per structure and purely latency bound (about 3 ms whatever the batch), so a
   // chunk is cut into sub-chunks: all front kernels are issued first on the caller's stream, each sub-chunk's k_ql runs on
@@ -558,5 +573,124 @@ extern "C" int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, 
   }
   if ((int64_t)n > max_elems) n = (size_t)max_elems;
   CUDA_TRY(cudaMemcpy(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// adjoint gradient
+// ---------------------------------------------------------------------------------------------------
+static constexpr int GTAIL_NT = 512, GEIG_NT = 256;
+
+template <typename K>
+static int plan_grad_kernel(pirl_handle* h, K kern, int nt, size_t vec_bytes, size_t mat_bytes, int want, int* mats,
+                            size_t* smem, int* grid) {
+  const size_t budget = h->smem_optin - 1024;
+  *mats = mats_that_fit(budget, vec_bytes, mat_bytes, want);
+  *smem = vec_bytes + (size_t)*mats * mat_bytes;
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+  CUDA_TRY(max_carveout(kern));
+  int per_sm = 0;
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, *smem));
+  if (per_sm < 1) return fail(-9, "gradient kernel does not fit on this device");
+  *grid = h->sm_count * per_sm;
+  return 0;
+}
+
+static int grad_prepare(pirl_handle* h) {
+  if (h->g_lamb) return 0;
+  const int ff = h->ff;
+  const size_t Bc = h->cfg.max_batch;
+  const size_t rmat = (size_t)ff * h->ld * sizeof(double), cmat = 2 * rmat;
+  int rc;
+  const size_t tvec = (size_t)grad_tail_vec_doubles(ff) * 8;
+  if (ff <= 96) rc = plan_grad_kernel(h, g_tail<GTAIL_NT, 3>, GTAIL_NT, tvec, cmat, 2, &h->g_tail_mats, &h->g_tail_smem, &h->g_tail_grid);
+  else if (ff <= 128) rc = plan_grad_kernel(h, g_tail<GTAIL_NT, 4>, GTAIL_NT, tvec, cmat, 2, &h->g_tail_mats, &h->g_tail_smem, &h->g_tail_grid);
+  else rc = plan_grad_kernel(h, g_tail<GTAIL_NT, 8>, GTAIL_NT, tvec, cmat, 2, &h->g_tail_mats, &h->g_tail_smem, &h->g_tail_grid);
+  if (rc) return rc;
+  rc = plan_grad_kernel(h, g_eigback<GEIG_NT>, GEIG_NT, (size_t)grad_eig_vec_doubles(ff, h->cfg.n_cells) * 8, rmat, 4,
+                        &h->g_eig_mats, &h->g_eig_smem, &h->g_eig_grid);
+  if (rc) return rc;
+  h->g_tail_stride = grad_tail_scratch_doubles(ff, h->ld);
+  h->g_eig_stride = grad_eig_scratch_doubles(ff, h->ld);
+  CUDA_TRY(dmalloc(&h->g_scr_tail, (size_t)h->g_tail_grid * h->g_tail_stride));
+  CUDA_TRY(dmalloc(&h->g_scr_eig, (size_t)h->g_eig_grid * h->g_eig_stride));
+  CUDA_TRY(dmalloc(&h->g_Lf, Bc * ff * PIRL_GRAD_RANK));
+  CUDA_TRY(dmalloc(&h->g_Rf, Bc * ff * PIRL_GRAD_RANK));
+  CUDA_TRY(dmalloc(&h->g_lamb, Bc * ff));
+  return 0;
+}
+
+extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                                   int64_t B, double* eff, double* grad, int32_t* status, void* stream) {
+  if (B == 0 && h) return 0;
+  if (!h || !patterns || !params || !eff || !grad) return fail(-1, "null argument");
+  if (B < 0) return fail(-2, "negative batch");
+  if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  if (int rc = grad_prepare(h)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t mb = h->cfg.max_batch;
+  const int ff = h->ff;
+  for (int64_t off = 0; off < B; off += mb) {
+    const int Bc = (int)std::min<int64_t>(mb, B - off);
+    KParams P = chunk_params(h, patterns + off * h->cfg.n_cells, params + off * param_stride, param_stride, Bc, eff + off,
+                             nullptr, nullptr, status ? status + off : nullptr);
+    GParams G;
+    G.lamb = h->g_lamb; G.Lf = h->g_Lf; G.Rf = h->g_Rf; G.grad = grad + off * h->cfg.n_cells;
+    launch_front(h, P, st);
+    launch_ql(h, P, st);
+    launch_apply(h, P, st);
+    {
+      StageTimer t(h, 7, st);
+      G.gscratch = h->g_scr_tail; G.gstride = h->g_tail_stride; G.smem_mats = h->g_tail_mats;
+      const int g = std::min(Bc, h->g_tail_grid);
+      if (ff <= 96) g_tail<GTAIL_NT, 3><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
+      else if (ff <= 128) g_tail<GTAIL_NT, 4><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
+      else g_tail<GTAIL_NT, 8><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
+    }
+    {
+      StageTimer t(h, 8, st);
+      G.gscratch = h->g_scr_eig; G.gstride = h->g_eig_stride; G.smem_mats = h->g_eig_mats;
+      g_eigback<GEIG_NT><<<std::min(Bc, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
+    }
+    h->launches += 2;
+    h->last_chunk = Bc;
+    CUDA_TRY(cudaGetLastError());
+  }
+  return 0;
+}
+
+extern "C" int pirl_rcwa_eval_grad_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                                        int64_t B, double* eff, double* grad, int32_t* status) {
+  if (B == 0 && h) return 0;
+  if (!h || !patterns || !params || !eff || !grad) return fail(-1, "null argument");
+  if (B < 0) return fail(-2, "negative batch");
+  if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const size_t nc = h->cfg.n_cells;
+  if (B > h->hd_cap) {
+    cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
+    h->hd_patterns = nullptr; h->hd_params = nullptr; h->hd_out = nullptr; h->hd_status = nullptr; h->hd_cap = 0;
+    CUDA_TRY(dmalloc(&h->hd_patterns, (size_t)B * nc));
+    CUDA_TRY(dmalloc(&h->hd_params, (size_t)B * 4));
+    CUDA_TRY(dmalloc(&h->hd_out, (size_t)B * 7));
+    CUDA_TRY(dmalloc(&h->hd_status, (size_t)B));
+    h->hd_cap = B;
+  }
+  if (B > h->hd_grad_cap) {
+    cudaFree(h->hd_grad); h->hd_grad = nullptr; h->hd_grad_cap = 0;
+    CUDA_TRY(dmalloc(&h->hd_grad, (size_t)B * nc));
+    h->hd_grad_cap = B;
+  }
+  cudaStream_t st = h->own_stream;
+  const size_t np = param_stride ? (size_t)B * 4 : 4;
+  CUDA_TRY(cudaMemcpyAsync(h->hd_patterns, patterns, (size_t)B * nc, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(h->hd_params, params, np * sizeof(double), cudaMemcpyHostToDevice, st));
+  int rc = pirl_rcwa_eval_grad(h, h->hd_patterns, h->hd_params, param_stride, B, h->hd_out, h->hd_grad, h->hd_status, st);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(eff, h->hd_out, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(grad, h->hd_grad, (size_t)B * nc * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (status) CUDA_TRY(cudaMemcpyAsync(status, h->hd_status, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
   return 0;
 }

@@ -1,0 +1,607 @@
+// rcwa_grad.cuh -- adjoint (reverse-mode) gradient d eff / d s_p of the batched RCWA evaluation.
+//
+// The reference has no gradient code; the contract is the central finite difference of the
+// reference forward solver w.r.t. a continuous pixel value (JLAB/solver.py:21-22 is affine in the cell value, the
+// permittivity and its reciprocal are taken pixel by pixel before convolution_matrix.py:89-114).  The reverse sweep is
+// validated step by step in tools/proto_grad.py.
+//
+// Two kernels after the forward front / QL / apply kernels have left W (A-orthonormal modes) and lambda in the workspaces:
+//   g_tail     forward layer solve (same algebra as k_tail) keeping P, Hq, H_II and the pivoted LU of S, then the reverse
+//              sweep of the layer solve.  Every adjoint of the layer solve is rank one or two (S-bar = -bb c+^H), so this is
+//              a dozen matrix-vector products; it emits lambda-bar and a rank-15 factorisation of Pm = W^T W-bar.
+//   g_eigback  reverse sweep of the generalised symmetric eigenproblem B w = lambda A w (three real GEMMs), of
+//              B = S_K^T E^-1 S_K - I and E^-1 (two GEMMs), Toeplitz-diagonal sums, inverse DFT to the pixels.
+//
+// Convention for a real objective f and a complex intermediate z: zbar = df/dRe z + i df/dIm z, df = Re(conj(zbar) dz).
+#pragma once
+#include "rcwa_kernels.cuh"
+
+#define PIRL_GRAD_RANK 16   // 15 used: 6 complex outer products (12 real) + 3 rows of W-bar
+
+struct GParams {
+  double* lamb;        // [B][ff]       d f / d lambda_j
+  double* Lf;          // [B][ff][16]   Pm = Lf Rf^T
+  double* Rf;          // [B][ff][16]
+  double* grad;        // [B][n_cells]  output
+  double* gscratch;    // per-CTA scratch (L2 resident)
+  size_t gstride;      // doubles per CTA
+  int smem_mats;       // matrices held in shared memory (kernel specific)
+};
+
+__host__ __device__ inline int grad_tail_vec_doubles(int ff) { return tail_vec_doubles(ff) + pirl_even(ff / 2 + 2); }
+// per-CTA scratch of g_tail (doubles): Hq, H_II complex [ff][ff]; two complex spill matrices [ff][ld]; 16 complex vectors
+__host__ __device__ inline size_t grad_tail_scratch_doubles(int ff, int ld) {
+  return 4 * (size_t)ff * ff + 4 * (size_t)ff * ld + 32 * (size_t)ff + 16;
+}
+// g_eigback shared vectors (doubles): lam, lamb, dpm, rowk, colk [ff]; cre, cim, gEr, gEi, gAr, gAi [2N+1 = ff]; pattern bits
+__host__ __device__ inline int grad_eig_vec_doubles(int ff, int n_cells) { return pirl_even(11 * ff + (n_cells + 7) / 8 + 2); }
+__host__ __device__ inline size_t grad_eig_scratch_doubles(int ff, int ld) { return 4 * (size_t)ff * ld + 16; }
+
+__device__ __forceinline__ cplx cconj(cplx a) { return make_double2(a.x, -a.y); }
+
+// y_i = sum_j M[i][j] x_j (+ diag_i x_i): one warp per row.  M complex symmetric in every use, so this also serves M^T x.
+template <int NT>
+__device__ __forceinline__ void cta_symv(const cplx* M, int ld, const cplx* x, cplx* y, int ff, const cplx* diag = nullptr) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = warp; i < ff; i += NT / 32) {
+    cplx s = make_double2(0.0, 0.0);
+    for (int j = lane; j < ff; j += 32) s = cfma(M[(size_t)i * ld + j], x[j], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      if (diag) s = cfma(diag[i], x[i], s);
+      y[i] = s;
+    }
+  }
+}
+
+// ===================================================================================================
+// g_tail : forward layer solve + its reverse sweep
+// ===================================================================================================
+template <int NT, int NCOL>
+__global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
+  extern __shared__ __align__(16) double sm[];
+  const int ff = P.ff, ld = P.ld, N = P.N, z = 2 * N;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = NT / 32;
+  cplx* qv = reinterpret_cast<cplx*>(sm);
+  cplx* Xv = qv + ff;
+  cplx* XQ = Xv + ff;
+  cplx* omx2 = XQ + ff;
+  cplx* DI = omx2 + ff;
+  cplx* DII = DI + ff;
+  cplx* rowk = DII + ff;
+  cplx* colk = rowk + ff;
+  cplx* bvec = colk + ff;
+  cplx* yv = bvec + ff;
+  cplx* dv = yv + ff;
+  double* wr = reinterpret_cast<double*>(dv + ff);  // [3][ff]
+  cplx* red = reinterpret_cast<cplx*>(wr + 3 * ff + ((3 * ff) & 1));
+  int* ipiv = reinterpret_cast<int*>(red + 32);     // [ff + 1]
+  double* mat0 = sm + grad_tail_vec_doubles(ff);
+  const size_t csz = (size_t)ff * ld;
+  double* scr = G.gscratch + (size_t)blockIdx.x * G.gstride;
+  cplx* Hq = reinterpret_cast<cplx*>(scr);          // [ff][ff] global (L2 resident)
+  cplx* HII = Hq + (size_t)ff * ff;
+  cplx* spill = HII + (size_t)ff * ff;
+  cplx* Pm = (G.smem_mats >= 1) ? reinterpret_cast<cplx*>(mat0) : spill;
+  cplx* Sm = (G.smem_mats >= 2) ? reinterpret_cast<cplx*>(mat0) + csz : spill + csz;
+  double* Wr = reinterpret_cast<double*>(Sm);
+  cplx* gv = spill + 2 * csz;                       // 16 global vectors
+  cplx* v_ell = gv;           cplx* v_x = gv + ff;       cplx* v_yb = gv + 2 * ff;  cplx* v_qb = gv + 3 * ff;
+  cplx* v_Xb = gv + 4 * ff;   cplx* v_hb = gv + 5 * ff;  cplx* v_w2 = gv + 6 * ff;  cplx* v_pw2 = gv + 7 * ff;
+  cplx* v_x2 = gv + 8 * ff;   cplx* v_pm = gv + 9 * ff;  cplx* v_in = gv + 10 * ff; /* 6 vectors: v_in .. v_in + 6 ff */
+
+  for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
+    __syncthreads();
+    const double* pr = P.params + (size_t)b * P.pstride;
+    const double wl = pr[0], ang = pr[1], thick = pr[2];
+    const double sa = sin(ang * (3.14159265358979323846 / 180.0));
+    const double k0d = 2.0 * 3.14159265358979323846 / wl * thick;
+    const double nI = P.n_inc, nII = P.n_exit;
+    const double* lamg = P.lam + (size_t)b * ff;
+    for (int t = tid; t < ff; t += NT) {
+      const double l = lamg[t];
+      cplx q, X;
+      if (l >= 0.0) { double s = sqrt(l); q = make_double2(s, 0.0); X = make_double2(exp(-k0d * s), 0.0); }
+      else { double s = sqrt(-l); q = make_double2(0.0, s); double sn, cs; sincos(k0d * s, &sn, &cs); X = make_double2(cs, -sn); }
+      qv[t] = q; Xv[t] = X; XQ[t] = cmul(X, q);
+      cplx x2 = cmul(X, X);
+      omx2[t] = make_double2(1.0 - x2.x, -x2.y);
+      const double kap = (t < z) ? ((t >> 1) + 1) * sa : 0.0;
+      const double aI = nI * nI - kap * kap, aII = nII * nII - kap * kap;
+      DI[t] = (aI >= 0.0) ? make_double2(0.0, sqrt(aI) / (nI * nI)) : make_double2(sqrt(-aI) / (nI * nI), 0.0);
+      DII[t] = (aII >= 0.0) ? make_double2(0.0, sqrt(aII) / (nII * nII)) : make_double2(sqrt(-aII) / (nII * nII), 0.0);
+    }
+    const double* Wg = P.Wbuf + (size_t)b * ff * ff;
+    for (int i = warp; i < ff; i += NW)
+      for (int j = lane; j < ff; j += 32) Wr[i * ld + j] = Wg[i * ff + j];
+    for (int t = tid; t < ff; t += NT) {
+      wr[t] = Wg[0 * ff + t];
+      wr[ff + t] = Wg[1 * ff + t];
+      wr[2 * ff + t] = Wg[(size_t)z * ff + t];
+    }
+    __syncthreads();
+    // ---- G_II -> Pm, Hq and H_II -> global ----
+    for (int i = warp; i < ff; i += NW) {
+      cplx aI[NCOL], aII[NCOL];
+#pragma unroll
+      for (int c = 0; c < NCOL; ++c) { aI[c] = make_double2(0.0, 0.0); aII[c] = make_double2(0.0, 0.0); }
+      for (int m = 0; m < ff; ++m) {
+        const double wi = Wr[m * ld + i];
+        const cplx d1 = DI[m], d2 = DII[m];
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) {
+          const int j = lane + 32 * c;
+          if (j < ff) {
+            const double pr2 = wi * Wr[m * ld + j];
+            aI[c].x = fma(d1.x, pr2, aI[c].x); aI[c].y = fma(d1.y, pr2, aI[c].y);
+            aII[c].x = fma(d2.x, pr2, aII[c].x); aII[c].y = fma(d2.y, pr2, aII[c].y);
+          }
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < NCOL; ++c) {
+        const int j = lane + 32 * c;
+        if (j < ff) {
+          cplx g = aII[c], h = aI[c];
+          HII[(size_t)i * ff + j] = g;
+          if (i == j) { g = cadd(g, qv[i]); h = csub(h, qv[i]); }
+          Pm[i * ld + j] = g;
+          Hq[(size_t)i * ff + j] = h;
+        }
+      }
+    }
+    // ---- P = G_II^-1 : complex symmetric Gauss-Jordan, no pivoting ----
+    for (int k = 0; k < ff; ++k) {
+      __syncthreads();
+      for (int t = tid; t < ff; t += NT) { rowk[t] = Pm[k * ld + t]; colk[t] = Pm[t * ld + k]; }
+      __syncthreads();
+      const cplx p = cinv(rowk[k]);
+      for (int i = warp; i < ff; i += NW) {
+        const cplx f = cmul(colk[i], p);
+        if (i == k) {
+          for (int j = lane; j < ff; j += 32) Pm[i * ld + j] = (j == k) ? p : cmul(rowk[j], p);
+        } else {
+          for (int j = lane; j < ff; j += 32)
+            Pm[i * ld + j] = (j == k) ? make_double2(-f.x, -f.y) : cfnma(f, rowk[j], Pm[i * ld + j]);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- S = Hq (I - X^2) + 2Q + 2 (Hq X) P (X Q) ----
+    for (int i = warp; i < ff; i += NW) {
+      cplx acc[NCOL];
+#pragma unroll
+      for (int c = 0; c < NCOL; ++c) acc[c] = make_double2(0.0, 0.0);
+      const cplx* hrow = Hq + (size_t)i * ff;
+      for (int k = 0; k < ff; ++k) {
+        const cplx f = cmul(hrow[k], Xv[k]);
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) {
+          const int j = lane + 32 * c;
+          if (j < ff) acc[c] = cfma(f, Pm[k * ld + j], acc[c]);
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < NCOL; ++c) {
+        const int j = lane + 32 * c;
+        if (j < ff) {
+          cplx s = cmul(acc[c], XQ[j]);
+          s = make_double2(2.0 * s.x, 2.0 * s.y);
+          s = cfma(hrow[j], omx2[j], s);
+          if (i == j) { s.x += 2.0 * qv[i].x; s.y += 2.0 * qv[i].y; }
+          Sm[i * ld + j] = s;
+        }
+      }
+    }
+    const cplx r0 = make_double2(DI[z].x, DI[z].y + 1.0 / nI);
+    for (int t = tid; t < ff; t += NT) bvec[t] = cscale(r0, wr[2 * ff + t]);
+    // ---- P_r S = L U with partial pivoting; multipliers kept below the diagonal, pivots in ipiv ----
+    for (int k = 0; k < ff; ++k) {
+      __syncthreads();
+      if (warp == 0) {
+        double best = -1.0; int bi = k;
+        for (int i = k + lane; i < ff; i += 32) {
+          cplx a = Sm[i * ld + k];
+          double mg = fabs(a.x) + fabs(a.y);
+          if (mg > best) { best = mg; bi = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          double ob = __shfl_xor_sync(0xffffffffu, best, o);
+          int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+          if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        }
+        if (lane == 0) ipiv[k] = bi;
+      }
+      __syncthreads();
+      const int pv = ipiv[k];
+      if (pv != k) {
+        for (int j = tid; j < ff; j += NT) { cplx t = Sm[k * ld + j]; Sm[k * ld + j] = Sm[pv * ld + j]; Sm[pv * ld + j] = t; }
+        if (tid == 0) { cplx t = bvec[k]; bvec[k] = bvec[pv]; bvec[pv] = t; }
+        __syncthreads();
+      }
+      const cplx pinv = cinv(Sm[k * ld + k]);
+      const cplx bk = bvec[k];
+      for (int i = k + 1 + warp; i < ff; i += NW) {
+        const cplx f = cmul(Sm[i * ld + k], pinv);
+        for (int j = k + 1 + lane; j < ff; j += 32) Sm[i * ld + j] = cfnma(f, Sm[k * ld + j], Sm[i * ld + j]);
+        if (lane == 0) { bvec[i] = cfnma(f, bk, bvec[i]); Sm[i * ld + k] = f; }
+      }
+    }
+    __syncthreads();
+    if (warp == 0) {   // back substitution U c+ = b'
+      for (int k = ff - 1; k >= 0; --k) {
+        cplx xk = cmul(bvec[k], cinv(Sm[k * ld + k]));
+        __syncwarp();
+        if (lane == 0) bvec[k] = xk;
+        for (int i = lane; i < k; i += 32) bvec[i] = cfnma(Sm[i * ld + k], xk, bvec[i]);
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    // ---- y = Q X c+,  d = 2 P y ----
+    for (int t = tid; t < ff; t += NT) yv[t] = cmul(XQ[t], bvec[t]);
+    __syncthreads();
+    cta_symv<NT>(Pm, ld, yv, dv, ff);
+    __syncthreads();
+    for (int t = tid; t < ff; t += NT) {
+      dv[t] = make_double2(2.0 * dv[t].x, 2.0 * dv[t].y);
+      v_ell[t] = make_double2(wr[t] * 0.7071067811865476, wr[ff + t] * 0.7071067811865476);   // order -1 = (cos1 + i sin1)/sqrt2
+    }
+    __syncthreads();
+    if (warp < 3) {   // T on {cos1, sin1, const}
+      cplx s = make_double2(0.0, 0.0);
+      for (int j = lane; j < ff; j += 32) { double w = wr[warp * ff + j]; s.x = fma(w, dv[j].x, s.x); s.y = fma(w, dv[j].y, s.y); }
+      s = warp_sum(s);
+      if (lane == 0) red[warp] = s;
+    }
+    __syncthreads();
+    const double is2 = 0.7071067811865476;
+    const cplx Tc = red[0], Ts = red[1], T0 = red[2];
+    const cplx Tm = make_double2((Tc.x - Ts.y) * is2, (Tc.y + Ts.x) * is2);
+    const double a1II = nII * nII - sa * sa;
+    const double k1II = a1II >= 0.0 ? sqrt(a1II) : 0.0;
+    const double alpha = k1II / (nII * nII) * nI;
+    const double eff = (Tm.x * Tm.x + Tm.y * Tm.y) * alpha;
+    if (tid == 0) {
+      int st = P.wstatus[b] & 0xff;
+      const double det1 = (T0.x * T0.x + T0.y * T0.y) * nI / nII;
+      if (!isfinite(eff) || !isfinite(det1)) st |= PIRL_ST_NONFINITE_;
+      P.eff[b] = eff;
+      if (P.status) P.status[b] = st;
+    }
+    // =============================== reverse sweep ===============================
+    double* Lf = G.Lf + (size_t)b * ff * PIRL_GRAD_RANK;
+    double* Rf = G.Rf + (size_t)b * ff * PIRL_GRAD_RANK;
+    const cplx tb = make_double2(2.0 * alpha * Tm.x, 2.0 * alpha * Tm.y);
+    for (int t = tid; t < ff; t += NT) {
+      const cplx el = v_ell[t];
+      v_x[t] = cmul(el, cconj(tb));                    // conj(d-bar),  d-bar = conj(ell) t-bar
+      const cplx ellb = cmul(cconj(dv[t]), tb);
+      Lf[t * PIRL_GRAD_RANK + 12] = wr[t];        Rf[t * PIRL_GRAD_RANK + 12] = ellb.x * is2;   // W-bar row cos1
+      Lf[t * PIRL_GRAD_RANK + 13] = wr[ff + t];   Rf[t * PIRL_GRAD_RANK + 13] = ellb.y * is2;   // W-bar row sin1
+      Lf[t * PIRL_GRAD_RANK + 15] = 0.0;          Rf[t * PIRL_GRAD_RANK + 15] = 0.0;
+    }
+    __syncthreads();
+    cta_symv<NT>(Pm, ld, v_x, v_yb, ff);               // P conj(d-bar);  y-bar = 2 conj(.)
+    __syncthreads();
+    for (int t = tid; t < ff; t += NT) {
+      const cplx yb = make_double2(2.0 * v_yb[t].x, -2.0 * v_yb[t].y);
+      v_yb[t] = yb;
+      const cplx cp = bvec[t];
+      v_qb[t] = cmul(cconj(cmul(Xv[t], cp)), yb);
+      v_Xb[t] = cmul(cconj(cmul(qv[t], cp)), yb);
+      rowk[t] = cmul(cconj(XQ[t]), yb);                // c+-bar : right-hand side of S^H bb = c+-bar
+    }
+    __syncthreads();
+    if (warp == 0) {
+      // U^H w = c (forward), L^H v = w (backward, unit diagonal), bb = P_r^T v (swaps in reverse order)
+      for (int k = 0; k < ff; ++k) {
+        cplx wk = cmul(rowk[k], cinv(cconj(Sm[k * ld + k])));
+        __syncwarp();
+        if (lane == 0) rowk[k] = wk;
+        for (int i = k + 1 + lane; i < ff; i += 32) rowk[i] = cfnma(cconj(Sm[k * ld + i]), wk, rowk[i]);
+        __syncwarp();
+      }
+      for (int k = ff - 1; k >= 1; --k) {
+        const cplx vk = rowk[k];
+        __syncwarp();
+        for (int i = lane; i < k; i += 32) rowk[i] = cfnma(cconj(Sm[k * ld + i]), vk, rowk[i]);
+        __syncwarp();
+      }
+      if (lane == 0)
+        for (int k = ff - 1; k >= 0; --k) {
+          const int pv = ipiv[k];
+          if (pv != k) { cplx t = rowk[k]; rowk[k] = rowk[pv]; rowk[pv] = t; }
+        }
+    }
+    __syncthreads();
+    for (int t = tid; t < ff; t += NT) {
+      const cplx bb = rowk[t];
+      Lf[t * PIRL_GRAD_RANK + 14] = wr[2 * ff + t];
+      Rf[t * PIRL_GRAD_RANK + 14] = bb.x * r0.x + bb.y * r0.y;    // Re(conj(bb) r0) : W-bar row const
+      v_x[t] = cconj(bb);
+      v_w2[t] = cscale(cmul(bvec[t], XQ[t]), 2.0);
+    }
+    __syncthreads();
+    cta_symv<NT>(Hq, ff, v_x, v_hb, ff);               // Hq conj(bb);  hb = Hq^H bb = conj(.)
+    cta_symv<NT>(Pm, ld, v_w2, v_pw2, ff);             // P w2
+    __syncthreads();
+    for (int t = tid; t < ff; t += NT) {
+      const cplx hq = v_hb[t];                         // = conj(hb)
+      v_x2[t] = cmul(Xv[t], hq);                       // conj(M1^H bb) = X conj(hb)
+    }
+    __syncthreads();
+    cta_symv<NT>(Pm, ld, v_x2, v_pm, ff);              // pm = P conj(m1hb)
+    __syncthreads();
+    double* lambg = G.lamb + (size_t)b * ff;
+    for (int t = tid; t < ff; t += NT) {
+      const cplx cp = bvec[t], bb = rowk[t], X = Xv[t], q = qv[t];
+      const cplx hb = cconj(v_hb[t]), pw2 = v_pw2[t], pm = v_pm[t], yb = v_yb[t];
+      cplx qb = v_qb[t], Xb = v_Xb[t];
+      const cplx ccp = cconj(cp);
+      // S-bar = -bb c+^H.  Hq D1 term:
+      const cplx D1b = cscale(cmul(ccp, hb), -1.0);
+      Xb = cfma(cscale(cconj(X), -2.0), D1b, Xb);
+      qb = cfma(cscale(bb, -2.0), ccp, qb);
+      // 2 (Hq X) P (X q) term:
+      const cplx xqb = cscale(cmul(ccp, cconj(pm)), -2.0);
+      Xb = cfma(cconj(q), xqb, Xb);
+      qb = cfma(cconj(X), xqb, qb);
+      const cplx h = cfma(X, pw2, cmul(cp, omx2[t]));
+      Xb = cfnma(hb, cconj(pw2), Xb);
+      qb = cfma(bb, cconj(h), qb);
+      // G-bar = g1a g1b^H + g2a g2b^H ;  g1a = -y-bar, g1b = d/2, g2a = conj(pm), g2b = pw2
+      const cplx g1a = cscale(yb, -1.0), g1b = cscale(dv[t], 0.5), g2a = cconj(pm), g2b = pw2;
+      qb = cfma(g1a, cconj(g1b), qb);
+      qb = cfma(g2a, cconj(g2b), qb);
+      qb = cfma(cscale(cconj(X), -k0d), Xb, qb);
+      double lb = 0.0;
+      if (q.y == 0.0) { if (q.x > 0.0) lb = qb.x / (2.0 * q.x); }
+      else lb = -qb.y / (2.0 * q.y);
+      lambg[t] = lb;
+      // rank-one pairs (H, a, c): H-bar = a c^H.  (H_I: a = -bb, c = h), (H_II: g1a, g1b), (H_II: g2a, g2b)
+      const cplx a1 = cscale(bb, -1.0);
+      v_in[t] = cconj(a1); v_in[ff + t] = h;
+      v_in[2 * ff + t] = cconj(g1a); v_in[3 * ff + t] = g1b;
+      v_in[4 * ff + t] = cconj(g2a); v_in[5 * ff + t] = g2b;
+      double* R = Rf + t * PIRL_GRAD_RANK;
+      R[0] = h.x;    R[1] = h.y;    R[2] = a1.x;   R[3] = -a1.y;
+      R[4] = g1b.x;  R[5] = g1b.y;  R[6] = g1a.x;  R[7] = -g1a.y;
+      R[8] = g2b.x;  R[9] = g2b.y;  R[10] = g2a.x; R[11] = -g2a.y;
+    }
+    __syncthreads();
+    // six products H x -> Lf columns (Re, -Im);  H_I = Hq + Q
+    for (int v = 0; v < 6; ++v) {
+      const cplx* M = (v < 2) ? Hq : HII;
+      const cplx* x = v_in + (size_t)v * ff;
+      for (int i = warp; i < ff; i += NW) {
+        cplx s = make_double2(0.0, 0.0);
+        for (int j = lane; j < ff; j += 32) s = cfma(M[(size_t)i * ff + j], x[j], s);
+        s = warp_sum(s);
+        if (lane == 0) {
+          if (v < 2) s = cfma(qv[i], x[i], s);
+          Lf[i * PIRL_GRAD_RANK + 2 * v] = s.x;
+          Lf[i * PIRL_GRAD_RANK + 2 * v + 1] = -s.y;
+        }
+      }
+    }
+  }
+}
+
+// ===================================================================================================
+// CTA-wide real GEMM on ff x ff matrices (shared memory or L2-resident scratch): C = A * B or A * B^T.
+// 16 x 16 threads, 6 x 6 register tile per thread (rows ty + 16 r, columns tx + 16 c) over 96 x 96 blocks of C.
+// C must not alias A or B.
+// ===================================================================================================
+template <bool TRANS_B>
+__device__ __forceinline__ void cta_gemm(double* __restrict__ C, const double* __restrict__ A, const double* __restrict__ B,
+                                         int ff, int ld) {
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  for (int i0 = 0; i0 < ff; i0 += 96)
+    for (int j0 = 0; j0 < ff; j0 += 96) {
+      double acc[6][6];
+      int ri[6], cj[6];
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        ri[r] = min(i0 + ty + 16 * r, ff - 1) * ld;
+        cj[r] = min(j0 + tx + 16 * r, ff - 1);
+        if (TRANS_B) cj[r] *= ld;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) acc[r][c] = 0.0;
+      }
+      for (int k = 0; k < ff; ++k) {
+        double a[6], bq[6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          a[r] = A[ri[r] + k];
+          bq[r] = TRANS_B ? B[cj[r] + k] : B[k * ld + cj[r]];
+        }
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+          for (int c = 0; c < 6; ++c) acc[r][c] = fma(a[r], bq[c], acc[r][c]);
+      }
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        const int i = i0 + ty + 16 * r;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          const int j = j0 + tx + 16 * c;
+          if (i < ff && j < ff) C[i * ld + j] = acc[r][c];
+        }
+      }
+    }
+}
+
+// adjoint of basis_toeplitz: accumulate sgn * Tb[i][j] * dT_ij/dc into (gr, gi) (shared, atomics)
+__device__ __forceinline__ void toeplitz_adjoint_add(int i, int j, int N, double v, double* gr, double* gi) {
+  const int z = 2 * N;
+  const double r2 = 1.4142135623730951;
+  if (i == z && j == z) { atomicAdd(&gr[0], v); return; }
+  if (i == z || j == z) {
+    const int o = (i == z) ? j : i;
+    const int p = (o >> 1) + 1;
+    if (o & 1) atomicAdd(&gi[p], -r2 * v); else atomicAdd(&gr[p], r2 * v);
+    return;
+  }
+  const int p = (i >> 1) + 1, q = (j >> 1) + 1;
+  const int d = p - q, ad = d < 0 ? -d : d;
+  const double sg = d >= 0 ? 1.0 : -1.0;
+  const int si = i & 1, sj = j & 1;
+  if (!si && !sj) { atomicAdd(&gr[ad], v); atomicAdd(&gr[p + q], v); }
+  else if (si && sj) { atomicAdd(&gr[ad], v); atomicAdd(&gr[p + q], -v); }
+  else if (!si && sj) { atomicAdd(&gi[p + q], -v); atomicAdd(&gi[ad], sg * v); }
+  else { atomicAdd(&gi[p + q], -v); atomicAdd(&gi[ad], -sg * v); }
+}
+
+// ===================================================================================================
+// g_eigback : reverse sweep through the generalised symmetric eigenproblem, B, E^-1, the Toeplitz maps and the DFT
+// ===================================================================================================
+template <int NT>
+__global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
+  static_assert(NT == 256, "cta_gemm assumes 16 x 16 threads");
+  extern __shared__ __align__(16) double sm[];
+  const int ff = P.ff, ld = P.ld, N = P.N, z = 2 * N, nc = P.n_cells;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = NT / 32;
+  double* lam = sm;
+  double* lamb = lam + ff;
+  double* dpm = lamb + ff;
+  double* rowk = dpm + ff;
+  double* colk = rowk + ff;
+  double* cre = colk + ff;
+  double* cim = cre + ff;
+  double* gEr = cim + ff;
+  double* gEi = gEr + ff;
+  double* gAr = gEi + ff;
+  double* gAi = gAr + ff;
+  uint8_t* su = reinterpret_cast<uint8_t*>(gAi + ff);
+  double* mat0 = sm + grad_eig_vec_doubles(ff, nc);
+  const size_t msz = (size_t)ff * ld;
+  double* scr = G.gscratch + (size_t)blockIdx.x * G.gstride;
+  double* M[4];
+  for (int m = 0; m < 4; ++m) M[m] = (m < G.smem_mats) ? mat0 + m * msz : scr + m * msz;
+  double *M0 = M[0], *M1 = M[1], *M2 = M[2], *M3 = M[3];
+
+  for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
+    __syncthreads();
+    const double* pr = P.params + (size_t)b * P.pstride;
+    const double ang = pr[1], nr = pr[3];
+    const double sa = sin(ang * (3.14159265358979323846 / 180.0));
+    const double er = nr * nr, eg = P.eps_g;
+    for (int t = tid; t < ff; t += NT) {
+      lam[t] = P.lam[(size_t)b * ff + t];
+      lamb[t] = G.lamb[(size_t)b * ff + t];
+      gEr[t] = 0.0; gEi[t] = 0.0; gAr[t] = 0.0; gAi[t] = 0.0;
+    }
+    for (int p = tid; p < nc; p += NT) su[p] = P.patterns[(size_t)b * nc + p] > 0;
+    __syncthreads();
+    for (int k = warp; k <= 2 * N; k += NW) {   // Fourier coefficients of the 0/1 pattern (as k_front)
+      double sx = 0.0, sy = 0.0;
+      for (int p = lane; p < nc; p += 32)
+        if (su[p]) { cplx t = __ldg(&P.tw[(k * p) % nc]); sx += t.x; sy += t.y; }
+      sx = warp_sum(sx); sy = warp_sum(sy);
+      if (lane == 0) {
+        cplx d = __ldg(&P.Dk[k]);
+        cre[k] = sx * d.x - sy * d.y;
+        cim[k] = sx * d.y + sy * d.x;
+      }
+    }
+    // ---- M0 = W ; M1 = Pm o F  (Pm = Lf Rf^T, F_ij = 1/(lam_j - lam_i), 0 on the diagonal and on degenerate pairs) ----
+    const double* Wg = P.Wbuf + (size_t)b * ff * ff;
+    const double* Lf = G.Lf + (size_t)b * ff * PIRL_GRAD_RANK;
+    const double* Rf = G.Rf + (size_t)b * ff * PIRL_GRAD_RANK;
+    for (int i = warp; i < ff; i += NW) {
+      double li[PIRL_GRAD_RANK];
+#pragma unroll
+      for (int r = 0; r < PIRL_GRAD_RANK; ++r) li[r] = Lf[i * PIRL_GRAD_RANK + r];
+      const double lmi = lam[i];
+      for (int j = lane; j < ff; j += 32) {
+        M0[i * ld + j] = Wg[i * ff + j];
+        double pm = 0.0;
+#pragma unroll
+        for (int r = 0; r < PIRL_GRAD_RANK; ++r) pm = fma(li[r], Rf[j * PIRL_GRAD_RANK + r], pm);
+        const double dl = lam[j] - lmi;
+        double v = 0.0;
+        if (i == j) dpm[i] = pm;
+        else if (fabs(dl) > 1e-9 * (fabs(lam[j]) + fabs(lmi))) v = pm / dl;
+        M1[i * ld + j] = v;
+      }
+    }
+    __syncthreads();
+    cta_gemm<false>(M2, M0, M1, ff, ld);                 // Z = W (Pm o F)
+    __syncthreads();
+    for (int i = warp; i < ff; i += NW)                  // Y_B = Z + W diag(lambda-bar)
+      for (int j = lane; j < ff; j += 32) M1[i * ld + j] = fma(M0[i * ld + j], lamb[j], M2[i * ld + j]);
+    __syncthreads();
+    cta_gemm<true>(M3, M1, M0, ff, ld);                  // B-bar = Y_B W^T
+    __syncthreads();
+    for (int i = warp; i < ff; i += NW)                  // Y_A = -(Z Lambda + W diag(lam lamb + Pm_jj / 2))
+      for (int j = lane; j < ff; j += 32)
+        M1[i * ld + j] = -fma(M2[i * ld + j], lam[j], M0[i * ld + j] * fma(lam[j], lamb[j], 0.5 * dpm[j]));
+    __syncthreads();
+    cta_gemm<true>(M2, M1, M0, ff, ld);                  // A-bar = Y_A W^T
+    __syncthreads();
+    for (int i = warp; i < ff; i += NW)
+      for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, M2[i * ld + j], gAr, gAi);
+    // ---- M0 = E^-1 (recomputed: Gauss-Jordan without pivoting, E is SPD) ----
+    {
+      const double de = er - eg;
+      for (int i = warp; i < ff; i += NW)
+        for (int j = lane; j < ff; j += 32)
+          M0[i * ld + j] = fma(de, basis_toeplitz(i, j, N, cre, cim), (i == j) ? eg : 0.0);
+    }
+    for (int k = 0; k < ff; ++k) {
+      __syncthreads();
+      for (int t = tid; t < ff; t += NT) { rowk[t] = M0[k * ld + t]; colk[t] = M0[t * ld + k]; }
+      __syncthreads();
+      const double p = 1.0 / rowk[k];
+      for (int i = warp; i < ff; i += NW) {
+        const double f = colk[i] * p;
+        if (i == k) {
+          for (int j = lane; j < ff; j += 32) M0[i * ld + j] = (j == k) ? p : rowk[j] * p;
+        } else {
+          for (int j = lane; j < ff; j += 32) M0[i * ld + j] = (j == k) ? -f : fma(-f, rowk[j], M0[i * ld + j]);
+        }
+      }
+    }
+    // ---- M1 = (E^-1)-bar = S_K B-bar S_K^T  (2x2 cos/sin blocks swap and change sign; constant row / column drop out) ----
+    for (int idx = tid; idx < N * N; idx += NT) {
+      const int pp = idx / N, qq = idx - pp * N;
+      const int ic = 2 * pp, is = ic + 1, jc = 2 * qq, js = jc + 1;
+      const double kk = ((pp + 1) * sa) * ((qq + 1) * sa);
+      M1[is * ld + js] = kk * M3[ic * ld + jc];
+      M1[is * ld + jc] = -kk * M3[ic * ld + js];
+      M1[ic * ld + js] = -kk * M3[is * ld + jc];
+      M1[ic * ld + jc] = kk * M3[is * ld + js];
+    }
+    for (int t = tid; t < ff; t += NT) { M1[z * ld + t] = 0.0; M1[t * ld + z] = 0.0; }
+    __syncthreads();
+    cta_gemm<false>(M2, M0, M1, ff, ld);
+    __syncthreads();
+    cta_gemm<false>(M3, M2, M0, ff, ld);                 // -E-bar = E^-1 (E^-1)-bar E^-1
+    __syncthreads();
+    for (int i = warp; i < ff; i += NW)
+      for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, -M3[i * ld + j], gEr, gEi);
+    __syncthreads();
+    // ---- g_k = conj(c-bar_k) D_k ; pixel gradient = Re sum_k g_k exp(-2 pi i k p / n) ----
+    for (int k = tid; k <= 2 * N; k += NT) {
+      const cplx d = __ldg(&P.Dk[k]);
+      const cplx e = cmul(make_double2(gEr[k], -gEi[k]), d), a = cmul(make_double2(gAr[k], -gAi[k]), d);
+      gEr[k] = e.x; gEi[k] = e.y; gAr[k] = a.x; gAi[k] = a.y;
+    }
+    __syncthreads();
+    for (int p = tid; p < nc; p += NT) {
+      double vE = 0.0, vA = 0.0;
+      for (int k = 0; k <= 2 * N; ++k) {
+        const cplx t = __ldg(&P.tw[(k * p) % nc]);
+        vE += gEr[k] * t.x - gEi[k] * t.y;
+        vA += gAr[k] * t.x - gAi[k] * t.y;
+      }
+      const double ep = su[p] ? er : eg;
+      G.grad[(size_t)b * nc + p] = 0.5 * (er - eg) * (vE - vA / (ep * ep));
+    }
+  }
+}

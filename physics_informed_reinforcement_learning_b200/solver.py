@@ -139,6 +139,49 @@ class RCWABatch:
             return eff, r3, t3, st
         return eff
 
+    def evaluate_grad(self, patterns, wavelength=1100.0, angle=60.0, thickness=325.0, n_ridge=None, params=None):
+        """Efficiency and its adjoint gradient d eff / d s_p.  patterns: torch int8 CUDA tensor [B, n_cells] of +-1.
+        Returns (eff [B], grad [B, n_cells], status [B]) as CUDA tensors, asynchronous on the current torch stream.
+        The reference has no gradient; the contract is the finite difference of its forward solver w.r.t. one continuous
+        cell value (solver.py:21-22), see ``pirl_rcwa_eval_grad`` in include/pirl_rcwa.h."""
+        torch = _torch()
+        if patterns.dtype != torch.int8 or not patterns.is_cuda or patterns.dim() != 2:
+            raise TypeError("patterns must be a 2-D int8 CUDA tensor")
+        if patterns.shape[1] != self.n_cells:
+            raise ValueError(f"expected {self.n_cells} cells per pattern")
+        patterns = patterns.contiguous()
+        B = patterns.shape[0]
+        dev = patterns.device
+        if params is None:
+            rows, stride = self._params(B, wavelength, angle, thickness, n_ridge)
+            params = torch.from_numpy(rows).to(dev, non_blocking=True)
+        else:
+            stride = 4 if params.shape[0] > 1 else 0
+        eff = torch.empty(B, dtype=torch.float64, device=dev)
+        grad = torch.empty(B, self.n_cells, dtype=torch.float64, device=dev)
+        st = torch.empty(B, dtype=torch.int32, device=dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(self.lib.pirl_rcwa_eval_grad(self._h, patterns.data_ptr(), params.data_ptr(), stride, B,
+                                                eff.data_ptr(), grad.data_ptr(), st.data_ptr(), C.c_void_p(stream)))
+        self._keep = (patterns, params)
+        return eff, grad, st
+
+    def evaluate_grad_host(self, patterns, wavelength=1100.0, angle=60.0, thickness=325.0, n_ridge=None):
+        """Host buffers in / out (``pirl_rcwa_eval_grad_host``): returns (eff [B], grad [B, n_cells], status [B]) as numpy."""
+        pat = np.asarray(patterns)
+        if pat.ndim != 2 or pat.shape[1] != self.n_cells:
+            raise ValueError(f"patterns must be [B, {self.n_cells}]")
+        if pat.dtype != np.int8 or not pat.flags.c_contiguous:
+            pat = np.ascontiguousarray(np.where(pat > 0, 1, -1).astype(np.int8))
+        B = pat.shape[0]
+        rows, stride = self._params(B, wavelength, angle, thickness, n_ridge)
+        eff = np.empty(B, dtype=np.float64)
+        grad = np.empty((B, self.n_cells), dtype=np.float64)
+        st = np.empty(B, dtype=np.int32)
+        _lib.check(self.lib.pirl_rcwa_eval_grad_host(self._h, pat.ctypes.data, rows.ctypes.data, stride, B,
+                                                     eff.ctypes.data, grad.ctypes.data, st.ctypes.data))
+        return eff, grad, st
+
     def launch_count(self) -> int:
         return int(self.lib.pirl_rcwa_launch_count(self._h))
 

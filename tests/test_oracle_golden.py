@@ -76,3 +76,15 @@ def test_fd_gradient_fixture(golden_dir):
 
 def test_material_interpolation():
     assert O.n_silicon_real(1100.0) == pytest.approx(3.551726470588235, abs=1e-14)
+
+
+def test_grad_golden_consistent_with_oracle_fd(golden_dir):
+    """tests/golden/grad_golden.npz (oracle/make_grad_golden.py) is the oracle's own finite difference; spot-check it and
+    the values recorded in SURVEY.md section 8c (G9)."""
+    g = np.load(os.path.join(golden_dir, "grad_golden.npz"))
+    n = "G7_blocks16_N40"
+    idx = [5, 100, 200]
+    got = O.fd_gradient(g[n + "/pattern"], idx)
+    np.testing.assert_allclose(got, g[n + "/fd_grad"][idx], rtol=2e-6, atol=2e-9)    # FD rounding noise ~ eps/h
+    np.testing.assert_allclose(got, [-7.3443880e-04, 3.6901669e-03, -1.6564464e-03], rtol=2e-6)
+    assert abs(O.efficiency(g[n + "/pattern"]) - float(g[n + "/eff"])) < 1e-12       # BLAS thread count changes the last digits
