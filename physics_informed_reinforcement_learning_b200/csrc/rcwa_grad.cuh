@@ -17,11 +17,13 @@
 #include "rcwa_kernels.cuh"
 
 #define PIRL_GRAD_RANK 16   // 15 used: 6 complex outer products (12 real) + 3 rows of W-bar
+#define PIRL_GRAD_NV 20     // doubles per mode in Vf: g1a g1b g2a g2b bb (h-2c+) -hb Pw2 c+ (ybar-2g2a)
 
 struct GParams {
   double* lamb;        // [B][ff]       d f / d lambda_j
   double* Lf;          // [B][ff][16]   Pm = Lf Rf^T
   double* Rf;          // [B][ff][16]
+  double* Vf;          // [B][ff][20]   ten complex vectors: rank-one adjoints of the diagonal matrices q, X, 1-X^2, Xq
   double* grad;        // [B][n_cells]  output
   double* gscratch;    // per-CTA scratch (L2 resident)
   size_t gstride;      // doubles per CTA
@@ -366,6 +368,14 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       v_in[t] = cconj(a1); v_in[ff + t] = h;
       v_in[2 * ff + t] = cconj(g1a); v_in[3 * ff + t] = g1b;
       v_in[4 * ff + t] = cconj(g2a); v_in[5 * ff + t] = g2b;
+      {   // adjoints of the diagonal matrices taken as full matrices (Daleckii-Krein form of the eigenvector sweep):
+          // q-bar = g1a g1b^H + g2a g2b^H + bb (h - 2 c+)^H ; X-bar = -hb (P w2)^H ; (1-X^2)-bar = -hb c+^H ; (Xq)-bar = (y-bar - 2 g2a) c+^H
+        cplx* V = reinterpret_cast<cplx*>(G.Vf + ((size_t)b * ff + t) * PIRL_GRAD_NV);
+        V[0] = g1a; V[1] = g1b; V[2] = g2a; V[3] = g2b; V[4] = bb;
+        V[5] = make_double2(h.x - 2.0 * cp.x, h.y - 2.0 * cp.y);
+        V[6] = cscale(hb, -1.0); V[7] = pw2; V[8] = cp;
+        V[9] = make_double2(yb.x - 2.0 * g2a.x, yb.y - 2.0 * g2a.y);
+      }
       double* R = Rf + t * PIRL_GRAD_RANK;
       R[0] = h.x;    R[1] = h.y;    R[2] = a1.x;   R[3] = -a1.y;
       R[4] = g1b.x;  R[5] = g1b.y;  R[6] = g1a.x;  R[7] = -g1a.y;
@@ -433,6 +443,28 @@ __device__ __forceinline__ void cta_gemm(double* __restrict__ C, const double* _
         }
       }
     }
+}
+
+// q = sqrt(lambda) (principal branch), X = exp(-k0 d q)
+__device__ __forceinline__ void mode_qx(double l, double k0d, cplx& q, cplx& X) {
+  if (l >= 0.0) { const double s = sqrt(l); q = make_double2(s, 0.0); X = make_double2(exp(-k0d * s), 0.0); }
+  else { const double s = sqrt(-l); q = make_double2(0.0, s); double sn, cs; sincos(k0d * s, &sn, &cs); X = make_double2(cs, -sn); }
+}
+// (exp(z) - 1)/z for Re z <= 0
+__device__ __forceinline__ cplx cexpm1_over_z(cplx z) {
+  if (z.x * z.x + z.y * z.y < 1e-4) {
+    cplx r = make_double2(1.0 / 720.0, 0.0);
+    r = cfma(r, z, make_double2(1.0 / 120.0, 0.0));
+    r = cfma(r, z, make_double2(1.0 / 24.0, 0.0));
+    r = cfma(r, z, make_double2(1.0 / 6.0, 0.0));
+    r = cfma(r, z, make_double2(0.5, 0.0));
+    r = cfma(r, z, make_double2(1.0, 0.0));
+    return r;
+  }
+  double sn, cs;
+  sincos(z.y, &sn, &cs);
+  const double e = exp(z.x);
+  return cmul(make_double2(e * cs - 1.0, e * sn), cinv(z));
 }
 
 // adjoint of basis_toeplitz: accumulate sgn * Tb[i][j] * dT_ij/dc into (gr, gi) (shared, atomics)
@@ -509,40 +541,88 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
         cim[k] = sx * d.y + sy * d.x;
       }
     }
-    // ---- M0 = W ; M1 = Pm o F  (Pm = Lf Rf^T, F_ij = 1/(lam_j - lam_i), 0 on the diagonal and on degenerate pairs) ----
+    // ---- M0 = W ; M1 = G_B ; M2 = G_A  (adjoints of B~ = W^T B W and A~ = W^T A W) ----
+    // dW = W Cm with Cm_ij = (dB~_ij - lam_j dA~_ij)/(lam_j - lam_i): the only singular combination is
+    // K_ij = (Pm_ij - Pm_ji)/(lam_j - lam_i).  The layer solve is invariant under W -> W R, diag(f(lam)) -> R^T diag(f) R,
+    // which gives K_ij = sum_f Re[conj(Phibar_f,ij + Phibar_f,ji) (f_j - f_i)/(lam_j - lam_i)] with stable divided differences
+    // (tools/proto_grad.py).  G_B = K/2 + diag(lambda-bar);  G_A = -(sym(Pm) + (lam_i + lam_j) K / 2)/2, diag -(lam lamb + Pm_jj/2).
     const double* Wg = P.Wbuf + (size_t)b * ff * ff;
     const double* Lf = G.Lf + (size_t)b * ff * PIRL_GRAD_RANK;
     const double* Rf = G.Rf + (size_t)b * ff * PIRL_GRAD_RANK;
+    const double* Vf = G.Vf + (size_t)b * ff * PIRL_GRAD_NV;
+    const double k0d = 2.0 * 3.14159265358979323846 / pr[0] * pr[2];
+    constexpr int NVEC = 2 * PIRL_GRAD_RANK + PIRL_GRAD_NV;   // 52 doubles per mode
+    if (ld >= NVEC) {   // stage the per-mode vectors in M3's storage (free until the first GEMM)
+      for (int idx = tid; idx < ff * PIRL_GRAD_RANK; idx += NT) { M3[idx] = Lf[idx]; M3[ff * PIRL_GRAD_RANK + idx] = Rf[idx]; }
+      for (int idx = tid; idx < ff * PIRL_GRAD_NV; idx += NT) M3[2 * ff * PIRL_GRAD_RANK + idx] = Vf[idx];
+      Lf = M3; Rf = M3 + ff * PIRL_GRAD_RANK; Vf = M3 + 2 * ff * PIRL_GRAD_RANK;
+      __syncthreads();
+    }
     for (int i = warp; i < ff; i += NW) {
-      double li[PIRL_GRAD_RANK];
+      double li[PIRL_GRAD_RANK], ri[PIRL_GRAD_RANK];
+      cplx vi[PIRL_GRAD_NV / 2];
 #pragma unroll
-      for (int r = 0; r < PIRL_GRAD_RANK; ++r) li[r] = Lf[i * PIRL_GRAD_RANK + r];
+      for (int r = 0; r < PIRL_GRAD_RANK; ++r) { li[r] = Lf[i * PIRL_GRAD_RANK + r]; ri[r] = Rf[i * PIRL_GRAD_RANK + r]; }
+#pragma unroll
+      for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vi[r] = make_double2(Vf[i * PIRL_GRAD_NV + 2 * r], Vf[i * PIRL_GRAD_NV + 2 * r + 1]);
       const double lmi = lam[i];
+      cplx qi, Xi;
+      mode_qx(lmi, k0d, qi, Xi);
       for (int j = lane; j < ff; j += 32) {
         M0[i * ld + j] = Wg[i * ff + j];
-        double pm = 0.0;
+        double pij = 0.0, pji = 0.0;
 #pragma unroll
-        for (int r = 0; r < PIRL_GRAD_RANK; ++r) pm = fma(li[r], Rf[j * PIRL_GRAD_RANK + r], pm);
-        const double dl = lam[j] - lmi;
-        double v = 0.0;
-        if (i == j) dpm[i] = pm;
-        else if (fabs(dl) > 1e-9 * (fabs(lam[j]) + fabs(lmi))) v = pm / dl;
-        M1[i * ld + j] = v;
+        for (int r = 0; r < PIRL_GRAD_RANK; ++r) {
+          pij = fma(li[r], Rf[j * PIRL_GRAD_RANK + r], pij);
+          pji = fma(ri[r], Lf[j * PIRL_GRAD_RANK + r], pji);
+        }
+        const double lmj = lam[j];
+        if (i == j) {
+          M1[i * ld + j] = lamb[i];
+          M2[i * ld + j] = -fma(lmi, lamb[i], 0.5 * pij);
+          continue;
+        }
+        cplx vj[PIRL_GRAD_NV / 2];   // (the staged copy is only 8-byte aligned: ff * ld is odd)
+#pragma unroll
+        for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vj[r] = make_double2(Vf[j * PIRL_GRAD_NV + 2 * r], Vf[j * PIRL_GRAD_NV + 2 * r + 1]);
+        cplx qj, Xj;
+        mode_qx(lmj, k0d, qj, Xj);
+        // S_f,ij = sum over pairs a_i conj(c_j) + a_j conj(c_i)
+        cplx Sq = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          Sq = cfma(vi[2 * r], cconj(vj[2 * r + 1]), Sq);
+          Sq = cfma(vj[2 * r], cconj(vi[2 * r + 1]), Sq);
+        }
+        const cplx mhi = vi[6], mhj = vj[6];
+        const cplx SX = cfma(mhi, cconj(vj[7]), cmul(mhj, cconj(vi[7])));
+        const cplx SD = cfma(mhi, cconj(vj[8]), cmul(mhj, cconj(vi[8])));
+        const cplx SXQ = cfma(vi[9], cconj(vj[8]), cmul(vj[9], cconj(vi[8])));
+        // divided differences (f_j - f_i)/(lam_j - lam_i)
+        const cplx dq = cinv(cadd(qi, qj));
+        cplx zz = make_double2(-k0d * (qj.x - qi.x), -k0d * (qj.y - qi.y));
+        cplx Xref = Xi;
+        if (zz.x > 0.0) { zz = make_double2(-zz.x, -zz.y); Xref = Xj; }
+        const cplx dX = cscale(cmul(cmul(Xref, cexpm1_over_z(zz)), dq), -k0d);
+        const cplx dD1 = cscale(cmul(cadd(Xi, Xj), dX), -1.0);
+        const cplx dXQ = cfma(Xj, dq, cmul(qi, dX));
+        cplx acc = cmul(cconj(Sq), dq);
+        acc = cfma(cconj(SX), dX, acc);
+        acc = cfma(cconj(SD), dD1, acc);
+        acc = cfma(cconj(SXQ), dXQ, acc);
+        const double K = acc.x;
+        M1[i * ld + j] = 0.5 * K;
+        M2[i * ld + j] = -0.5 * fma(0.5 * (lmi + lmj), K, 0.5 * (pij + pji));
       }
     }
     __syncthreads();
-    cta_gemm<false>(M2, M0, M1, ff, ld);                 // Z = W (Pm o F)
+    cta_gemm<false>(M3, M0, M1, ff, ld);                 // W G_B
     __syncthreads();
-    for (int i = warp; i < ff; i += NW)                  // Y_B = Z + W diag(lambda-bar)
-      for (int j = lane; j < ff; j += 32) M1[i * ld + j] = fma(M0[i * ld + j], lamb[j], M2[i * ld + j]);
+    cta_gemm<true>(M1, M3, M0, ff, ld);                  // B-bar = W G_B W^T
     __syncthreads();
-    cta_gemm<true>(M3, M1, M0, ff, ld);                  // B-bar = Y_B W^T
+    cta_gemm<false>(M3, M0, M2, ff, ld);                 // W G_A
     __syncthreads();
-    for (int i = warp; i < ff; i += NW)                  // Y_A = -(Z Lambda + W diag(lam lamb + Pm_jj / 2))
-      for (int j = lane; j < ff; j += 32)
-        M1[i * ld + j] = -fma(M2[i * ld + j], lam[j], M0[i * ld + j] * fma(lam[j], lamb[j], 0.5 * dpm[j]));
-    __syncthreads();
-    cta_gemm<true>(M2, M1, M0, ff, ld);                  // A-bar = Y_A W^T
+    cta_gemm<true>(M2, M3, M0, ff, ld);                  // A-bar = W G_A W^T
     __syncthreads();
     for (int i = warp; i < ff; i += NW)
       for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, M2[i * ld + j], gAr, gAi);
@@ -572,19 +652,19 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
       const int pp = idx / N, qq = idx - pp * N;
       const int ic = 2 * pp, is = ic + 1, jc = 2 * qq, js = jc + 1;
       const double kk = ((pp + 1) * sa) * ((qq + 1) * sa);
-      M1[is * ld + js] = kk * M3[ic * ld + jc];
-      M1[is * ld + jc] = -kk * M3[ic * ld + js];
-      M1[ic * ld + js] = -kk * M3[is * ld + jc];
-      M1[ic * ld + jc] = kk * M3[is * ld + js];
+      M3[is * ld + js] = kk * M1[ic * ld + jc];
+      M3[is * ld + jc] = -kk * M1[ic * ld + js];
+      M3[ic * ld + js] = -kk * M1[is * ld + jc];
+      M3[ic * ld + jc] = kk * M1[is * ld + js];
     }
-    for (int t = tid; t < ff; t += NT) { M1[z * ld + t] = 0.0; M1[t * ld + z] = 0.0; }
+    for (int t = tid; t < ff; t += NT) { M3[z * ld + t] = 0.0; M3[t * ld + z] = 0.0; }
     __syncthreads();
-    cta_gemm<false>(M2, M0, M1, ff, ld);
+    cta_gemm<false>(M2, M0, M3, ff, ld);
     __syncthreads();
-    cta_gemm<false>(M3, M2, M0, ff, ld);                 // -E-bar = E^-1 (E^-1)-bar E^-1
+    cta_gemm<false>(M1, M2, M0, ff, ld);                 // -E-bar = E^-1 (E^-1)-bar E^-1
     __syncthreads();
     for (int i = warp; i < ff; i += NW)
-      for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, -M3[i * ld + j], gEr, gEi);
+      for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, -M1[i * ld + j], gEr, gEi);
     __syncthreads();
     // ---- g_k = conj(c-bar_k) D_k ; pixel gradient = Re sum_k g_k exp(-2 pi i k p / n) ----
     for (int k = tid; k <= 2 * N; k += NT) {
