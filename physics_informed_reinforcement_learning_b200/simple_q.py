@@ -1,0 +1,210 @@
+"""Native SimpleQ loop over the vectorised deflector env.
+
+Replaces the un-vendored RLlib driver of the reference (main.py:146-186, configs/simple_q.py:47-82) with a thin PyTorch loop
+around the unchanged Q-network hook; the env physics is the batched RCWA backend.  Hyper-parameters are the reference's
+``multiple_worker`` config: epsilon-greedy 0.99 -> 0.01 over 100 k timesteps, replay 100 k with learning start at 1000,
+train batch 512, Adam lr 1e-3, gamma 0.99, target update every 2000 timesteps with tau 0.1, 128-step episodes
+(main.py:139 TimeLimit).  RLlib's exact loss/replay internals are not in the reference tree -> RL-loop parity is unpinned
+(SURVEY.md section 8c); what is pinned and tested is the env transition and the hyper-parameter schedule.
+
+Multi-GPU (one process per GPU): envs and replay are rank-local; ranks stay in lock step by averaging gradients
+(``all_reduce``) after an initial ``broadcast`` of the policy weights; ``max_efficiency`` is reduced with MAX.  No env data
+crosses GPUs.
+"""
+from __future__ import annotations
+
+import copy
+import dataclasses
+import os
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+from torch import nn
+
+
+@dataclasses.dataclass
+class SimpleQConfig:
+    gamma: float = 0.99                        # configs/simple_q.py:67
+    lr: float = 1e-3                           # :66
+    train_batch_size: int = 512                # :68 (global, split over ranks)
+    replay_capacity: int = 100_000             # :60
+    learning_starts: int = 1000                # :59
+    target_network_update_freq: int = 2000     # :53
+    tau: float = 0.1                           # :69
+    initial_epsilon: float = 0.99              # :78
+    final_epsilon: float = 0.01                # :79
+    epsilon_timesteps: int = 100_000           # :80
+    train_every: int = 1                       # learner updates per vector-env step
+    seed: int = 42                             # utils.py:14-18 seed_all
+
+
+def epsilon_at(cfg: SimpleQConfig, timestep: int) -> float:
+    """Linear schedule of RLlib's EpsilonGreedy (PiecewiseSchedule between (0, initial) and (epsilon_timesteps, final))."""
+    f = min(max(timestep / float(cfg.epsilon_timesteps), 0.0), 1.0)
+    return cfg.initial_epsilon + f * (cfg.final_epsilon - cfg.initial_epsilon)
+
+
+class DeviceReplay:
+    """Uniform ring buffer resident on the env's device: obs / next_obs as int8 patterns (256 B per transition)."""
+
+    def __init__(self, capacity: int, n_cells: int, device):
+        self.capacity, self.size, self.pos = int(capacity), 0, 0
+        self.obs = torch.empty(capacity, n_cells, dtype=torch.int8, device=device)
+        self.next_obs = torch.empty(capacity, n_cells, dtype=torch.int8, device=device)
+        self.action = torch.empty(capacity, dtype=torch.int64, device=device)
+        self.reward = torch.empty(capacity, dtype=torch.float32, device=device)
+        self.done = torch.empty(capacity, dtype=torch.bool, device=device)
+
+    def add(self, obs, action, reward, next_obs, done):
+        n = obs.shape[0]
+        idx = (torch.arange(n, device=obs.device) + self.pos) % self.capacity
+        self.obs[idx] = obs.to(torch.int8)
+        self.next_obs[idx] = next_obs.to(torch.int8)
+        self.action[idx] = action
+        self.reward[idx] = reward.to(torch.float32)
+        self.done[idx] = done
+        self.pos = (self.pos + n) % self.capacity
+        self.size = min(self.size + n, self.capacity)
+
+    def sample(self, batch: int, generator=None):
+        idx = torch.randint(0, self.size, (batch,), device=self.obs.device, generator=generator)
+        return self.obs[idx], self.action[idx], self.reward[idx], self.next_obs[idx], self.done[idx]
+
+
+class SimpleQTrainer:
+    """env: object with ``B``, ``n_cells``, ``device``, ``reset() -> obs[B,n]``, ``step(actions) -> (obs, reward, done, info)``
+    and ``best_eff`` (``VectorDeflectorEnv`` or a test double)."""
+
+    def __init__(self, env, model: nn.Module, cfg: SimpleQConfig | None = None, log_dir: str | None = None):
+        self.env, self.cfg = env, cfg or SimpleQConfig()
+        self.device = torch.device(env.device) if not isinstance(env.device, torch.device) else env.device
+        self.model = model.to(self.device)
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        if self.world > 1:
+            for p in list(self.model.parameters()) + list(self.model.buffers()):
+                dist.broadcast(p.data, src=0)          # policy weights: rank 0 -> all
+        self.target = copy.deepcopy(self.model).eval()
+        for p in self.target.parameters():
+            p.requires_grad_(False)
+        self.opt = torch.optim.Adam(self.model.parameters(), lr=self.cfg.lr)
+        self.replay = DeviceReplay(max(self.cfg.replay_capacity // self.world, env.B), env.n_cells, self.device)
+        self.gen = torch.Generator(device=self.device)
+        self.gen.manual_seed(self.cfg.seed + 1000 * self.rank)
+        self.timesteps = 0            # global env steps (all ranks)
+        self.updates = 0
+        self.last_target_sync = 0
+        self.log_dir = log_dir
+        self.obs = None
+        self.max_efficiency = float("-inf")
+        self.timers = {"env": 0.0, "act": 0.0, "learn": 0.0}
+
+    # --------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def act(self, obs, epsilon: float):
+        self.model.eval()
+        q = self.model(obs.to(torch.float32))
+        greedy = q.argmax(dim=1)
+        rnd = torch.randint(0, q.shape[1], greedy.shape, device=q.device, generator=self.gen)
+        explore = torch.rand(greedy.shape, device=q.device, generator=self.gen) < epsilon
+        return torch.where(explore, rnd, greedy)
+
+    def learn(self):
+        cfg = self.cfg
+        b = max(cfg.train_batch_size // self.world, 1)
+        obs, act, rew, nxt, done = self.replay.sample(b, self.gen)
+        self.model.train()
+        q = self.model(obs.to(torch.float32)).gather(1, act[:, None]).squeeze(1)
+        with torch.no_grad():
+            qn = self.target(nxt.to(torch.float32)).max(dim=1).values
+            tgt = rew + cfg.gamma * (~done).to(torch.float32) * qn
+        loss = nn.functional.huber_loss(q, tgt)
+        self.opt.zero_grad(set_to_none=True)
+        loss.backward()
+        if self.world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in self.model.parameters() if p.grad is not None])
+            dist.all_reduce(flat)
+            flat /= self.world
+            o = 0
+            for p in self.model.parameters():
+                if p.grad is not None:
+                    n = p.grad.numel()
+                    p.grad.copy_(flat[o:o + n].view_as(p.grad))
+                    o += n
+        self.opt.step()
+        self.updates += 1
+        return loss.detach()
+
+    @torch.no_grad()
+    def sync_target(self):
+        tau = self.cfg.tau
+        for pt, p in zip(self.target.parameters(), self.model.parameters()):
+            pt.mul_(1.0 - tau).add_(p, alpha=tau)
+        for bt, b in zip(self.target.buffers(), self.model.buffers()):
+            bt.copy_(b)
+
+    # --------------------------------------------------------------------------------------------
+    def train(self, total_timesteps: int, log_every: int = 0):
+        """Runs until ``total_timesteps`` GLOBAL env steps have been taken.  Returns a metrics dict."""
+        env, cfg = self.env, self.cfg
+        if self.obs is None:
+            np.random.seed(cfg.seed + self.rank)
+            torch.manual_seed(cfg.seed + self.rank)
+            self.obs = env.reset()
+        per_iter = env.B * self.world
+        losses = []
+        sync = (lambda: torch.cuda.synchronize(self.device)) if self.device.type == "cuda" else (lambda: None)
+        t_start = time.perf_counter()
+        it = 0
+        while self.timesteps < total_timesteps:
+            eps = epsilon_at(cfg, self.timesteps)
+            t0 = time.perf_counter()
+            actions = self.act(self.obs, eps)
+            sync(); t1 = time.perf_counter()
+            nxt, reward, done, info = env.step(actions)
+            # with auto-reset the returned obs of a finished env is the first obs of the next episode; the transition stored
+            # is (s, a, r, s', done) with s' = the flipped pattern, reconstructed from s and a
+            s_next = self.obs.clone().to(torch.int8)
+            inb = (actions >= 0) & (actions < env.n_cells)
+            rows = torch.nonzero(inb).squeeze(1)
+            s_next[rows, actions[rows]] = -s_next[rows, actions[rows]]
+            self.replay.add(self.obs, actions, reward, s_next, done.to(torch.bool))
+            self.obs = nxt
+            sync(); t2 = time.perf_counter()
+            self.timesteps += per_iter
+            if self.replay.size * self.world >= cfg.learning_starts:
+                for _ in range(cfg.train_every):
+                    losses.append(self.learn())
+                if self.timesteps - self.last_target_sync >= cfg.target_network_update_freq:
+                    self.sync_target()
+                    self.last_target_sync = self.timesteps
+            sync(); t3 = time.perf_counter()
+            self.timers["act"] += t1 - t0; self.timers["env"] += t2 - t1; self.timers["learn"] += t3 - t2
+            it += 1
+            if log_every and it % log_every == 0 and self.rank == 0:
+                print(f"[simple_q] t={self.timesteps} eps={eps:.3f} max_eff={float(env.best_eff.max()):.4f} "
+                      f"loss={float(losses[-1]) if losses else float('nan'):.3e}", flush=True)
+        wall = time.perf_counter() - t_start
+        best = env.best_eff.max().to(torch.float64).reshape(1).clone()
+        if self.world > 1:
+            dist.all_reduce(best, op=dist.ReduceOp.MAX)
+        self.max_efficiency = float(best)
+        total = sum(self.timers.values()) or 1.0
+        return {"timesteps": self.timesteps, "updates": self.updates, "max_efficiency": self.max_efficiency,
+                "env_steps_per_s": it * per_iter / wall, "wall_s": wall,
+                "time_fraction": {k: v / total for k, v in self.timers.items()},
+                "final_loss": float(losses[-1]) if losses else None, "epsilon": epsilon_at(cfg, self.timesteps)}
+
+    def save_best(self):
+        """main.py:80-85: dump the best structure of this rank as .npy, file name from eff * 100."""
+        if not self.log_dir:
+            return None
+        os.makedirs(self.log_dir, exist_ok=True)
+        i = int(self.env.best_eff.argmax())
+        eff = float(self.env.best_eff[i])
+        name = "w" + str(self.rank) + f"_{eff * 100:.6f}".replace(".", "-")
+        path = os.path.join(self.log_dir, name)
+        np.save(path, self.env.best_patterns[i].to(torch.float64).cpu().numpy())
+        return path + ".npy"

@@ -1,0 +1,65 @@
+#!/usr/bin/env python
+"""RL training entry point: the reference's ``python main.py`` (main.py:88-187) over the B200-native vectorised env.
+
+    python train.py --wavelength 1100 --angle 60 --thickness 325 --train_steps 200000 --num_envs 1024
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 train.py --num_envs 1024
+
+``--num_envs`` is the GLOBAL number of vectorised envs (config C3: 1024 = 128 per GPU x 8); each rank owns num_envs / world
+of them, its own RCWA handle and replay shard.  The Q-network is the unchanged UNet hook (qnet.ShallowUQNet); a pretrained
+state_dict is loaded when ``--pretrained_ckpt`` exists (the reference's file is not shipped: .MISSING_LARGE_BLOBS).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+
+import torch
+import torch.distributed as dist
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--wavelength", type=int, default=1100)
+    ap.add_argument("--angle", type=int, default=60)
+    ap.add_argument("--thickness", type=int, default=325)
+    ap.add_argument("--order", type=int, default=40)
+    ap.add_argument("--n_cells", type=int, default=256)
+    ap.add_argument("--train_steps", type=int, default=200000)
+    ap.add_argument("--num_envs", type=int, default=1024)
+    ap.add_argument("--max_episode_steps", type=int, default=128)
+    ap.add_argument("--pretrained_ckpt", type=str, default="pretrained/pretrained_1100nm_60degree.pt")
+    ap.add_argument("--model", choices=["unet", "fcn", "fcn_heavy"], default="unet")
+    ap.add_argument("--data_dir", type=str, default="runs/simple_q")
+    ap.add_argument("--log_every", type=int, default=50)
+    ap.add_argument("--seed", type=int, default=42)
+    args = ap.parse_args()
+
+    from physics_informed_reinforcement_learning_b200 import VectorDeflectorEnv
+    from physics_informed_reinforcement_learning_b200.qnet import ShallowUQNet, FCNQNet, load_pretrained
+    from physics_informed_reinforcement_learning_b200.simple_q import SimpleQConfig, SimpleQTrainer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank = dist.get_rank() if world > 1 else 0
+    per_rank = max(args.num_envs // world, 1)
+    env = VectorDeflectorEnv(per_rank, n_cells=args.n_cells, wavelength=args.wavelength, desired_angle=args.angle,
+                             order=args.order, thickness=args.thickness, max_episode_steps=args.max_episode_steps, device=local)
+    model = {"unet": lambda: ShallowUQNet(args.n_cells), "fcn": lambda: FCNQNet(args.n_cells),
+             "fcn_heavy": lambda: FCNQNet(args.n_cells, 1200)}[args.model]()
+    loaded = load_pretrained(model, args.pretrained_ckpt)
+    trainer = SimpleQTrainer(env, model, SimpleQConfig(seed=args.seed), log_dir=args.data_dir)
+    out = trainer.train(args.train_steps, log_every=args.log_every)
+    path = trainer.save_best()
+    if rank == 0:
+        out.update({"world": world, "envs_per_rank": per_rank, "pretrained_loaded": loaded, "best_structure": path})
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
