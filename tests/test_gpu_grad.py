@@ -129,3 +129,27 @@ def test_empty_batch_and_argument_errors(pkg, torch_mod):
     with pytest.raises(ValueError):
         be.evaluate_grad(torch.zeros(2, 100, dtype=torch.int8, device="cuda"))
     be.close()
+
+
+def test_wavelength_angle_sweep_forward_and_gradient(pkg, torch_mod):
+    """Config C4 shape (order 60, grid of wavelengths x angles, per-structure parameter rows) at a reduced grid, against the oracle."""
+    torch = torch_mod
+    from oracle import rcwa_oracle
+    from physics_informed_reinforcement_learning_b200.sweep import sweep
+    rng = np.random.default_rng(4)
+    pats = np.repeat(rng.choice([-1, 1], (3, 32)), 8, axis=1).astype(np.int8)
+    wls, angs = [900.0, 1050.0, 1200.0], [50.0, 65.0, 75.0]
+    be = pkg.RCWABatch(256, 60, max_batch=16, device=0)          # max_batch < 27 cells: exercises chunking with per-row parameters
+    eff, grad, st = sweep(be, torch.from_numpy(pats).cuda(), wls, angs, grad=True)
+    eff_f = sweep(be, torch.from_numpy(pats).cuda(), wls, angs)
+    torch.cuda.synchronize()
+    assert eff.shape == (3, 3, 3) and grad.shape == (3, 3, 3, 256) and int(st.abs().sum()) == 0
+    assert float((eff - eff_f).abs().max()) <= 1e-10
+    eff = eff.cpu().numpy(); grad = grad.cpu().numpy()
+    for (p, i, j) in [(0, 0, 0), (1, 1, 2), (2, 2, 1), (0, 2, 2)]:
+        ref = rcwa_oracle.efficiency(pats[p].astype(np.float64), wls[i], angs[j], 60, 325.0)
+        assert abs(eff[p, i, j] - ref) <= 1e-9, (p, i, j, eff[p, i, j], ref)
+        idx = [3, 120, 250]
+        fd = rcwa_oracle.fd_gradient(pats[p].astype(np.float64), idx, wls[i], angs[j], 60, 325.0)
+        assert _close(grad[p, i, j, idx], fd).all(), (p, i, j, grad[p, i, j, idx], fd)
+    be.close()
