@@ -293,6 +293,25 @@ def run_b200(args):
     assert int(np.abs(hs).sum()) == 0, "solver status flags set"
     assert np.array_equal(he, eff.cpu().numpy()), "host entry and device entry disagree"
 
+    # ---- adjoint-gradient leg (not part of `value`): pirl_rcwa_eval_grad on the same batch, device resident ----------
+    grad_info = None
+    if not args.no_grad:
+        for _ in range(2):
+            be.evaluate_grad(d_pats, params=d_params)
+        torch.cuda.synchronize()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        gl0 = be.launch_count()
+        gsteps = min(args.steps, 3)
+        g0.record()
+        for _ in range(gsteps):
+            geff, ggrad, gst = be.evaluate_grad(d_pats, params=d_params)
+        g1.record()
+        torch.cuda.synchronize()
+        gms = g0.elapsed_time(g1) / gsteps
+        assert float((geff - eff).abs().max()) <= 1e-9, "gradient entry point disagrees with the forward entry point"
+        grad_info = {"value": args.batch / (gms * 1e-3), "unit": "gradients/s per GPU (efficiency + d eff / d 256 cells)",
+                     "ms_per_step": gms, "gpu_launches": int(be.launch_count() - gl0), "steps": gsteps}
+
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -317,8 +336,19 @@ def run_b200(args):
     flops_per_launch = STAGE_FLOPS_FF3.get(name, 0.0) * ff ** 3 * structs_per_launch
     achieved = flops_per_launch / per_launch_s / 1e12
     stage_total = sum(v[0] for v in stage.values())
+    # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/ncu_traffic.json), scaled to
+    # this run's structures per launch; null when no capture of that kernel is committed
+    traffic = None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as fh:
+            t = json.load(fh).get(name)
+        if t:
+            traffic = (t["dram_read_bytes"] + t["dram_write_bytes"]) * structs_per_launch / t["structures_per_launch"]
+    except (OSError, ValueError, KeyError):
+        traffic = None
     roofline = {"bound": "tensor", "kernel": name, "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
-                "frac": achieved / fp64_peak, "traffic": None,
+                "frac": achieved / fp64_peak, "traffic": traffic,
+                "algorithmic_bytes_per_launch": (args.n_cells + 8) * structs_per_launch,
                 "peak_source": "FP64: cuBLAS DGEMM 8192^3 best of 6 measured in this run (MEASURED_PEAKS.json has no FP64 row)",
                 "flops_per_launch": flops_per_launch, "ms_per_launch": per_launch_s * 1e3,
                 "share_of_step": ms / stage_total if stage_total else None,
@@ -339,6 +369,8 @@ def run_b200(args):
             "parity_max_abs_err_vs_cpu": parity}
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if grad_info is not None:
+        line["adjoint_grad"] = grad_info
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -359,6 +391,7 @@ def main():
     ap.add_argument("--thickness", type=float, default=325.0)
     ap.add_argument("--cpu-budget", type=float, default=10.0, help="seconds of wall time for the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-grad", action="store_true", help="skip the adjoint-gradient leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

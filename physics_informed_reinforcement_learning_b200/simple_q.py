@@ -36,7 +36,8 @@ class SimpleQConfig:
     initial_epsilon: float = 0.99              # :78
     final_epsilon: float = 0.01                # :79
     epsilon_timesteps: int = 100_000           # :80
-    train_every: int = 1                       # learner updates per vector-env step
+    timesteps_per_update: int = 32             # :71-73: 16 rollout workers x rollout_fragment_length 2 sampled per train batch
+    max_updates_per_iter: int = 64             # cap on learner updates after one vector-env step (B * world timesteps)
     seed: int = 42                             # utils.py:14-18 seed_all
 
 
@@ -96,6 +97,7 @@ class SimpleQTrainer:
         self.timesteps = 0            # global env steps (all ranks)
         self.updates = 0
         self.last_target_sync = 0
+        self.learn_credit_from = None   # timestep at which learning started (updates owed are counted from here)
         self.log_dir = log_dir
         self.obs = None
         self.max_efficiency = float("-inf")
@@ -175,7 +177,10 @@ class SimpleQTrainer:
             sync(); t2 = time.perf_counter()
             self.timesteps += per_iter
             if self.replay.size * self.world >= cfg.learning_starts:
-                for _ in range(cfg.train_every):
+                if self.learn_credit_from is None:
+                    self.learn_credit_from = self.timesteps - per_iter
+                owed = (self.timesteps - self.learn_credit_from) // max(cfg.timesteps_per_update, 1) - self.updates
+                for _ in range(int(min(max(owed, 1), cfg.max_updates_per_iter))):
                     losses.append(self.learn())
                 if self.timesteps - self.last_target_sync >= cfg.target_network_update_freq:
                     self.sync_target()
