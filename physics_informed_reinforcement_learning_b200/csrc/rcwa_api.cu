@@ -67,7 +67,7 @@ struct pirl_handle {
   int64_t hd_cap = 0;
   cudaStream_t own_stream = nullptr;
   // adjoint gradient (allocated on the first pirl_rcwa_eval_grad)
-  double *g_lamb = nullptr, *g_Lf = nullptr, *g_Rf = nullptr, *g_Vf = nullptr, *g_scr_tail = nullptr, *g_scr_eig = nullptr;
+  double *g_lamb = nullptr, *g_Lf = nullptr, *g_Rf = nullptr, *g_Vf = nullptr, *g_Einv = nullptr, *g_scr_tail = nullptr, *g_scr_eig = nullptr;
   int g_tail_grid = 0, g_tail_mats = 0, g_eig_grid = 0, g_eig_mats = 0;
   size_t g_tail_smem = 0, g_eig_smem = 0, g_tail_stride = 0, g_eig_stride = 0;
   double* hd_grad = nullptr; int64_t hd_grad_cap = 0;
@@ -304,7 +304,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
   cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace);
   cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
-  cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_Vf); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
+  cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_Vf); cudaFree(h->g_Einv); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
   for (auto e : h->evF) if (e) cudaEventDestroy(e);
@@ -617,6 +617,7 @@ static int grad_prepare(pirl_handle* h) {
   CUDA_TRY(dmalloc(&h->g_Lf, Bc * ff * PIRL_GRAD_RANK));
   CUDA_TRY(dmalloc(&h->g_Rf, Bc * ff * PIRL_GRAD_RANK));
   CUDA_TRY(dmalloc(&h->g_Vf, Bc * ff * PIRL_GRAD_NV));
+  CUDA_TRY(dmalloc(&h->g_Einv, Bc * ff * ff));
   CUDA_TRY(dmalloc(&h->g_lamb, Bc * ff));
   return 0;
 }
@@ -636,6 +637,7 @@ extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const
     const int Bc = (int)std::min<int64_t>(mb, B - off);
     KParams P = chunk_params(h, patterns + off * h->cfg.n_cells, params + off * param_stride, param_stride, Bc, eff + off,
                              nullptr, nullptr, status ? status + off : nullptr);
+    P.Einv = h->g_Einv;
     GParams G;
     G.lamb = h->g_lamb; G.Lf = h->g_Lf; G.Rf = h->g_Rf; G.Vf = h->g_Vf; G.grad = grad + off * h->cfg.n_cells;
     launch_front(h, P, st);

@@ -14,7 +14,7 @@
 //
 // Convention for a real objective f and a complex intermediate z: zbar = df/dRe z + i df/dIm z, df = Re(conj(zbar) dz).
 #pragma once
-#include "rcwa_kernels.cuh"
+#include "rcwa_regtile.cuh"
 
 #define PIRL_GRAD_RANK 16   // 15 used: 6 complex outer products (12 real) + 3 rows of W-bar
 #define PIRL_GRAD_NV 20     // doubles per mode in Vf: g1a g1b g2a g2b bb (h-2c+) -hb Pw2 c+ (ybar-2g2a)
@@ -30,13 +30,13 @@ struct GParams {
   int smem_mats;       // matrices held in shared memory (kernel specific)
 };
 
-__host__ __device__ inline int grad_tail_vec_doubles(int ff) { return tail_vec_doubles(ff) + pirl_even(ff / 2 + 2); }
+__host__ __device__ inline int grad_tail_vec_doubles(int ff) { return tail_vec_doubles(ff) + pirl_even(ff / 2 + 2) + pirl_even(ff); }
 // per-CTA scratch of g_tail (doubles): Hq, H_II complex [ff][ff]; two complex spill matrices [ff][ld]; 16 complex vectors
 __host__ __device__ inline size_t grad_tail_scratch_doubles(int ff, int ld) {
   return 4 * (size_t)ff * ff + 4 * (size_t)ff * ld + 32 * (size_t)ff + 16;
 }
-// g_eigback shared vectors (doubles): lam, lamb, dpm, rowk, colk [ff]; cre, cim, gEr, gEi, gAr, gAi [2N+1 = ff]; pattern bits
-__host__ __device__ inline int grad_eig_vec_doubles(int ff, int n_cells) { return pirl_even(11 * ff + (n_cells + 7) / 8 + 2); }
+// g_eigback shared vectors (doubles): lam, lamb, dpm, rowk, colk [ff]; cre, cim, gEr, gEi, gAr, gAi [2N+1 = ff]; q, X complex [ff]; pattern bits
+__host__ __device__ inline int grad_eig_vec_doubles(int ff, int n_cells) { return pirl_even(15 * ff + (n_cells + 7) / 8 + 2); }
 __host__ __device__ inline size_t grad_eig_scratch_doubles(int ff, int ld) { return 4 * (size_t)ff * ld + 16; }
 
 __device__ __forceinline__ cplx cconj(cplx a) { return make_double2(a.x, -a.y); }
@@ -54,6 +54,133 @@ __device__ __forceinline__ void cta_symv(const cplx* M, int ld, const cplx* x, c
       y[i] = s;
     }
   }
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// Complex register tiles for the dense steps of g_tail (ff <= 96, 512 threads = 16 warps): warp w owns rows w + 16 a
+// (a < RA), lane l owns columns l + 32 c (c < CC).  Per elimination step only the pivot row and column pass through shared
+// memory (RA + CC complex loads per RA * CC complex FMAs) instead of the whole matrix.
+// ---------------------------------------------------------------------------------------------------
+template <int RA, int CC>
+__device__ __forceinline__ void ctile_store(const cplx (&t)[RA][CC], cplx* M, int ld, int ff, int w, int lane) {
+#pragma unroll
+  for (int a = 0; a < RA; ++a) {
+    const int i = w + 16 * a;
+#pragma unroll
+    for (int c = 0; c < CC; ++c) {
+      const int j = lane + 32 * c;
+      if (i < ff && j < ff) M[i * ld + j] = t[a][c];
+    }
+  }
+}
+
+// in-place inverse by Gauss-Jordan without pivoting (complex symmetric G with a dominant diagonal)
+template <int RA, int CC>
+__device__ __forceinline__ void ctile_gj_inverse(cplx (&t)[RA][CC], cplx* rowk, cplx* colk, int ff, int w, int lane) {
+  for (int k = 0; k < ff; ++k) {
+    const int ka = k >> 4, kw = k & 15, kc = k >> 5, kl = k & 31;
+    __syncthreads();
+    if (w == kw) {
+#pragma unroll
+      for (int a = 0; a < RA; ++a)
+        if (a == ka) {
+#pragma unroll
+          for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; if (j < ff) rowk[j] = t[a][c]; }
+        }
+    }
+    if (lane == kl) {
+#pragma unroll
+      for (int c = 0; c < CC; ++c)
+        if (c == kc) {
+#pragma unroll
+          for (int a = 0; a < RA; ++a) { const int i = w + 16 * a; if (i < ff) colk[i] = t[a][c]; }
+        }
+    }
+    __syncthreads();
+    const cplx piv = rowk[k];
+    const cplx p = cinv(piv);
+    cplx rv[CC];
+#pragma unroll
+    for (int c = 0; c < CC; ++c) {
+      const int j = lane + 32 * c;
+      rv[c] = (j < ff) ? ((j == k) ? make_double2(1.0 + piv.x, piv.y) : rowk[j]) : make_double2(0.0, 0.0);
+    }
+#pragma unroll
+    for (int a = 0; a < RA; ++a) {
+      const int i = w + 16 * a;
+      cplx cv = make_double2(0.0, 0.0);
+      if (i < ff) cv = (i == k) ? make_double2(p.x - 1.0, p.y) : cscale(cmul(colk[i], p), -1.0);
+#pragma unroll
+      for (int c = 0; c < CC; ++c) t[a][c] = cfma(cv, rv[c], t[a][c]);
+    }
+  }
+  __syncthreads();
+}
+
+// LU with implicit partial pivoting: rows are never moved; rperm[k] = pivot row of step k.  Multipliers are left in column k
+// of the rows still unused, the pivot rows hold U.  The right-hand side bvec (shared) is eliminated alongside.
+template <int RA, int CC>
+__device__ __forceinline__ void ctile_lu_implicit(cplx (&t)[RA][CC], cplx* rowk, cplx* colk, double* magk, cplx* bvec, int* rperm,
+                                                  int ff, int w, int lane) {
+  unsigned used = 0;
+#pragma unroll
+  for (int a = 0; a < RA; ++a) if (w + 16 * a >= ff) used |= 1u << a;
+  for (int k = 0; k < ff; ++k) {
+    const int kc = k >> 5, kl = k & 31;
+    __syncthreads();
+    if (lane == kl) {
+#pragma unroll
+      for (int c = 0; c < CC; ++c)
+        if (c == kc) {
+#pragma unroll
+          for (int a = 0; a < RA; ++a) {
+            const int i = w + 16 * a;
+            if (i < ff) { colk[i] = t[a][c]; magk[i] = ((used >> a) & 1u) ? -1.0 : fabs(t[a][c].x) + fabs(t[a][c].y); }
+          }
+        }
+    }
+    __syncthreads();
+    // every warp finds the same pivot (largest |re| + |im| among the unused rows, lowest row on ties)
+    double best = -2.0; int pv = 0;
+    for (int i = lane; i < ff; i += 32) { const double m = magk[i]; if (m > best) { best = m; pv = i; } }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, pv, o);
+      if (ob > best || (ob == best && oi < pv)) { best = ob; pv = oi; }
+    }
+    const int pa = pv >> 4, pw = pv & 15;
+    if (w == pw) {
+#pragma unroll
+      for (int a = 0; a < RA; ++a)
+        if (a == pa) {
+#pragma unroll
+          for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; if (j < ff) rowk[j] = t[a][c]; }
+        }
+      used |= 1u << pa;
+      if (lane == 0) rperm[k] = pv;
+    }
+    __syncthreads();
+    const cplx pinv = cinv(rowk[k]);
+    const cplx bk = bvec[pv];
+    cplx rv[CC];
+#pragma unroll
+    for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; rv[c] = (j < ff && j > k) ? rowk[j] : make_double2(0.0, 0.0); }
+#pragma unroll
+    for (int a = 0; a < RA; ++a) {
+      if ((used >> a) & 1u) continue;          // warp-uniform
+      const int i = w + 16 * a;
+      const cplx f = cmul(colk[i], pinv);
+#pragma unroll
+      for (int c = 0; c < CC; ++c) {
+        t[a][c] = cfnma(f, rv[c], t[a][c]);
+        if (lane + 32 * c == k) t[a][c] = f;
+      }
+      if (lane == 0) bvec[i] = cfnma(f, bk, bvec[i]);
+    }
+  }
+  __syncthreads();
 }
 
 // ===================================================================================================
@@ -79,6 +206,9 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
   double* wr = reinterpret_cast<double*>(dv + ff);  // [3][ff]
   cplx* red = reinterpret_cast<cplx*>(wr + 3 * ff + ((3 * ff) & 1));
   int* ipiv = reinterpret_cast<int*>(red + 32);     // [ff + 1]
+  double* magk = sm + tail_vec_doubles(ff) + pirl_even(ff / 2 + 2);   // [ff] pivot magnitudes; later the inverse row permutation
+  constexpr bool REG = (NCOL == 3) && (NT == 512);  // complex register tiles for ff <= 96
+  constexpr int RA = REG ? 6 : 1;
   double* mat0 = sm + grad_tail_vec_doubles(ff);
   const size_t csz = (size_t)ff * ld;
   double* scr = G.gscratch + (size_t)blockIdx.x * G.gstride;
@@ -101,6 +231,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     const double k0d = 2.0 * 3.14159265358979323846 / wl * thick;
     const double nI = P.n_inc, nII = P.n_exit;
     const double* lamg = P.lam + (size_t)b * ff;
+    long long pc_ = clock64();
     for (int t = tid; t < ff; t += NT) {
       const double l = lamg[t];
       cplx q, X;
@@ -123,6 +254,89 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       wr[2 * ff + t] = Wg[(size_t)z * ff + t];
     }
     __syncthreads();
+    const cplx r0 = make_double2(DI[z].x, DI[z].y + 1.0 / nI);
+    if constexpr (REG) {
+      cplx tl[RA][NCOL];
+      // ---- G_II -> register tile, Hq and H_II -> global ----
+#pragma unroll
+      for (int a = 0; a < RA; ++a) {
+        const int i = warp + 16 * a;
+        cplx aI[NCOL], aII[NCOL];
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) { aI[c] = make_double2(0.0, 0.0); aII[c] = make_double2(0.0, 0.0); }
+        if (i < ff) {
+          for (int m = 0; m < ff; ++m) {
+            const double wi = Wr[m * ld + i];
+            const cplx d1 = DI[m], d2 = DII[m];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) {
+              const int j = min(lane + 32 * c, ff - 1);
+              const double pr2 = wi * Wr[m * ld + j];
+              aI[c].x = fma(d1.x, pr2, aI[c].x); aI[c].y = fma(d1.y, pr2, aI[c].y);
+              aII[c].x = fma(d2.x, pr2, aII[c].x); aII[c].y = fma(d2.y, pr2, aII[c].y);
+            }
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) {
+          const int j = lane + 32 * c;
+          cplx g = aII[c], h = aI[c];
+          if (i < ff && j < ff) {
+            HII[(size_t)i * ff + j] = g;
+            if (i == j) { g = cadd(g, qv[i]); h = csub(h, qv[i]); }
+            Hq[(size_t)i * ff + j] = h;
+          }
+          tl[a][c] = g;
+        }
+      }
+      RK_PHASE(16);
+      ctile_gj_inverse<RA, NCOL>(tl, rowk, colk, ff, warp, lane);
+      ctile_store<RA, NCOL>(tl, Pm, ld, ff, warp, lane);
+      __syncthreads();
+      RK_PHASE(17);
+      // ---- S = Hq (I - X^2) + 2Q + 2 (Hq X) P (X Q) -> register tile ----
+#pragma unroll
+      for (int a = 0; a < RA; ++a) {
+        const int i = warp + 16 * a;
+        cplx acc[NCOL];
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) acc[c] = make_double2(0.0, 0.0);
+        const cplx* hrow = Hq + (size_t)min(i, ff - 1) * ff;
+        if (i < ff) {
+          for (int k = 0; k < ff; ++k) {
+            const cplx f = cmul(hrow[k], Xv[k]);
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) acc[c] = cfma(f, Pm[k * ld + min(lane + 32 * c, ff - 1)], acc[c]);
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) {
+          const int j = min(lane + 32 * c, ff - 1);
+          cplx sv = cmul(acc[c], XQ[j]);
+          sv = make_double2(2.0 * sv.x, 2.0 * sv.y);
+          sv = cfma(hrow[j], omx2[j], sv);
+          if (i == j) { sv.x += 2.0 * qv[j].x; sv.y += 2.0 * qv[j].y; }
+          tl[a][c] = sv;
+        }
+      }
+      RK_PHASE(18);
+      for (int t = tid; t < ff; t += NT) bvec[t] = cscale(r0, wr[2 * ff + t]);
+      ctile_lu_implicit<RA, NCOL>(tl, rowk, colk, magk, bvec, ipiv, ff, warp, lane);
+      // rows out in pivot order: P_r S = L U in the usual layout; b' = P_r b
+      int* pos = reinterpret_cast<int*>(magk);
+      for (int k = tid; k < ff; k += NT) { pos[ipiv[k]] = k; colk[k] = bvec[ipiv[k]]; }
+      __syncthreads();
+#pragma unroll
+      for (int a = 0; a < RA; ++a) {
+        const int i = warp + 16 * a;
+        if (i < ff) {
+          const int pr_ = pos[i];
+#pragma unroll
+          for (int c = 0; c < NCOL; ++c) { const int j = lane + 32 * c; if (j < ff) Sm[pr_ * ld + j] = tl[a][c]; }
+        }
+      }
+      for (int k = tid; k < ff; k += NT) bvec[k] = colk[k];
+    } else {
     // ---- G_II -> Pm, Hq and H_II -> global ----
     for (int i = warp; i < ff; i += NW) {
       cplx aI[NCOL], aII[NCOL];
@@ -154,6 +368,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       }
     }
     // ---- P = G_II^-1 : complex symmetric Gauss-Jordan, no pivoting ----
+    RK_PHASE(16);
     for (int k = 0; k < ff; ++k) {
       __syncthreads();
       for (int t = tid; t < ff; t += NT) { rowk[t] = Pm[k * ld + t]; colk[t] = Pm[t * ld + k]; }
@@ -171,6 +386,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     }
     __syncthreads();
     // ---- S = Hq (I - X^2) + 2Q + 2 (Hq X) P (X Q) ----
+    RK_PHASE(17);
     for (int i = warp; i < ff; i += NW) {
       cplx acc[NCOL];
 #pragma unroll
@@ -196,7 +412,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
         }
       }
     }
-    const cplx r0 = make_double2(DI[z].x, DI[z].y + 1.0 / nI);
+    RK_PHASE(18);
     for (int t = tid; t < ff; t += NT) bvec[t] = cscale(r0, wr[2 * ff + t]);
     // ---- P_r S = L U with partial pivoting; multipliers kept below the diagonal, pivots in ipiv ----
     for (int k = 0; k < ff; ++k) {
@@ -231,6 +447,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
         if (lane == 0) { bvec[i] = cfnma(f, bk, bvec[i]); Sm[i * ld + k] = f; }
       }
     }
+    }
     __syncthreads();
     if (warp == 0) {   // back substitution U c+ = b'
       for (int k = ff - 1; k >= 0; --k) {
@@ -243,6 +460,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     }
     __syncthreads();
     // ---- y = Q X c+,  d = 2 P y ----
+    RK_PHASE(19);
     for (int t = tid; t < ff; t += NT) yv[t] = cmul(XQ[t], bvec[t]);
     __syncthreads();
     cta_symv<NT>(Pm, ld, yv, dv, ff);
@@ -274,6 +492,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       if (P.status) P.status[b] = st;
     }
     // =============================== reverse sweep ===============================
+    RK_PHASE(20);
     double* Lf = G.Lf + (size_t)b * ff * PIRL_GRAD_RANK;
     double* Rf = G.Rf + (size_t)b * ff * PIRL_GRAD_RANK;
     const cplx tb = make_double2(2.0 * alpha * Tm.x, 2.0 * alpha * Tm.y);
@@ -312,11 +531,17 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
         for (int i = lane; i < k; i += 32) rowk[i] = cfnma(cconj(Sm[k * ld + i]), vk, rowk[i]);
         __syncwarp();
       }
-      if (lane == 0)
+      if constexpr (REG) {        // bb[rperm[k]] = v[k]
+        __syncwarp();
+        for (int k = lane; k < ff; k += 32) colk[ipiv[k]] = rowk[k];
+        __syncwarp();
+        for (int k = lane; k < ff; k += 32) rowk[k] = colk[k];
+      } else if (lane == 0) {
         for (int k = ff - 1; k >= 0; --k) {
           const int pv = ipiv[k];
           if (pv != k) { cplx t = rowk[k]; rowk[k] = rowk[pv]; rowk[pv] = t; }
         }
+      }
     }
     __syncthreads();
     for (int t = tid; t < ff; t += NT) {
@@ -382,6 +607,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       R[8] = g2b.x;  R[9] = g2b.y;  R[10] = g2a.x; R[11] = -g2a.y;
     }
     __syncthreads();
+    RK_PHASE(21);
     // six products H x -> Lf columns (Re, -Im);  H_I = Hq + Q
     for (int v = 0; v < 6; ++v) {
       const cplx* M = (v < 2) ? Hq : HII;
@@ -397,6 +623,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
         }
       }
     }
+    RK_PHASE(22);
   }
 }
 
@@ -501,15 +728,13 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
   double* lam = sm;
   double* lamb = lam + ff;
   double* dpm = lamb + ff;
-  double* rowk = dpm + ff;
-  double* colk = rowk + ff;
-  double* cre = colk + ff;
-  double* cim = cre + ff;
-  double* gEr = cim + ff;
+  double* gEr = dpm + 5 * ff;   // (four spare vectors)
   double* gEi = gEr + ff;
   double* gAr = gEi + ff;
   double* gAi = gAr + ff;
-  uint8_t* su = reinterpret_cast<uint8_t*>(gAi + ff);
+  cplx* qS = reinterpret_cast<cplx*>(gAi + ff + (ff & 1));   // ff odd: keep the complex vectors 16-byte aligned
+  cplx* XS = qS + ff;
+  uint8_t* su = reinterpret_cast<uint8_t*>(XS + ff);
   double* mat0 = sm + grad_eig_vec_doubles(ff, nc);
   const size_t msz = (size_t)ff * ld;
   double* scr = G.gscratch + (size_t)blockIdx.x * G.gstride;
@@ -523,6 +748,7 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     const double ang = pr[1], nr = pr[3];
     const double sa = sin(ang * (3.14159265358979323846 / 180.0));
     const double er = nr * nr, eg = P.eps_g;
+    long long pc_ = clock64();
     for (int t = tid; t < ff; t += NT) {
       lam[t] = P.lam[(size_t)b * ff + t];
       lamb[t] = G.lamb[(size_t)b * ff + t];
@@ -530,17 +756,6 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     }
     for (int p = tid; p < nc; p += NT) su[p] = P.patterns[(size_t)b * nc + p] > 0;
     __syncthreads();
-    for (int k = warp; k <= 2 * N; k += NW) {   // Fourier coefficients of the 0/1 pattern (as k_front)
-      double sx = 0.0, sy = 0.0;
-      for (int p = lane; p < nc; p += 32)
-        if (su[p]) { cplx t = __ldg(&P.tw[(k * p) % nc]); sx += t.x; sy += t.y; }
-      sx = warp_sum(sx); sy = warp_sum(sy);
-      if (lane == 0) {
-        cplx d = __ldg(&P.Dk[k]);
-        cre[k] = sx * d.x - sy * d.y;
-        cim[k] = sx * d.y + sy * d.x;
-      }
-    }
     // ---- M0 = W ; M1 = G_B ; M2 = G_A  (adjoints of B~ = W^T B W and A~ = W^T A W) ----
     // dW = W Cm with Cm_ij = (dB~_ij - lam_j dA~_ij)/(lam_j - lam_i): the only singular combination is
     // K_ij = (Pm_ij - Pm_ji)/(lam_j - lam_i).  The layer solve is invariant under W -> W R, diag(f(lam)) -> R^T diag(f) R,
@@ -552,29 +767,40 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     const double* Vf = G.Vf + (size_t)b * ff * PIRL_GRAD_NV;
     const double k0d = 2.0 * 3.14159265358979323846 / pr[0] * pr[2];
     constexpr int NVEC = 2 * PIRL_GRAD_RANK + PIRL_GRAD_NV;   // 52 doubles per mode
+    for (int t = tid; t < ff; t += NT) mode_qx(lam[t], k0d, qS[t], XS[t]);
+    // element (mode m, component r) of the factor arrays: base[m * sm_ + r * sr_].  Staged copies are component-major
+    // (consecutive modes in consecutive banks); the global originals are mode-major.
+    int fsm = PIRL_GRAD_RANK, fsr = 1, vsm = PIRL_GRAD_NV, vsr = 1;
     if (ld >= NVEC) {   // stage the per-mode vectors in M3's storage (free until the first GEMM)
-      for (int idx = tid; idx < ff * PIRL_GRAD_RANK; idx += NT) { M3[idx] = Lf[idx]; M3[ff * PIRL_GRAD_RANK + idx] = Rf[idx]; }
-      for (int idx = tid; idx < ff * PIRL_GRAD_NV; idx += NT) M3[2 * ff * PIRL_GRAD_RANK + idx] = Vf[idx];
+      for (int idx = tid; idx < ff * PIRL_GRAD_RANK; idx += NT) {
+        const int m = idx / PIRL_GRAD_RANK, r = idx - m * PIRL_GRAD_RANK;
+        M3[r * ff + m] = Lf[idx];
+        M3[ff * PIRL_GRAD_RANK + r * ff + m] = Rf[idx];
+      }
+      for (int idx = tid; idx < ff * PIRL_GRAD_NV; idx += NT) {
+        const int m = idx / PIRL_GRAD_NV, r = idx - m * PIRL_GRAD_NV;
+        M3[2 * ff * PIRL_GRAD_RANK + r * ff + m] = Vf[idx];
+      }
       Lf = M3; Rf = M3 + ff * PIRL_GRAD_RANK; Vf = M3 + 2 * ff * PIRL_GRAD_RANK;
-      __syncthreads();
+      fsm = 1; fsr = ff; vsm = 1; vsr = ff;
     }
+    __syncthreads();
     for (int i = warp; i < ff; i += NW) {
       double li[PIRL_GRAD_RANK], ri[PIRL_GRAD_RANK];
       cplx vi[PIRL_GRAD_NV / 2];
 #pragma unroll
-      for (int r = 0; r < PIRL_GRAD_RANK; ++r) { li[r] = Lf[i * PIRL_GRAD_RANK + r]; ri[r] = Rf[i * PIRL_GRAD_RANK + r]; }
+      for (int r = 0; r < PIRL_GRAD_RANK; ++r) { li[r] = Lf[i * fsm + r * fsr]; ri[r] = Rf[i * fsm + r * fsr]; }
 #pragma unroll
-      for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vi[r] = make_double2(Vf[i * PIRL_GRAD_NV + 2 * r], Vf[i * PIRL_GRAD_NV + 2 * r + 1]);
+      for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vi[r] = make_double2(Vf[i * vsm + 2 * r * vsr], Vf[i * vsm + (2 * r + 1) * vsr]);
       const double lmi = lam[i];
-      cplx qi, Xi;
-      mode_qx(lmi, k0d, qi, Xi);
+      const cplx qi = qS[i], Xi = XS[i];
       for (int j = lane; j < ff; j += 32) {
         M0[i * ld + j] = Wg[i * ff + j];
         double pij = 0.0, pji = 0.0;
 #pragma unroll
         for (int r = 0; r < PIRL_GRAD_RANK; ++r) {
-          pij = fma(li[r], Rf[j * PIRL_GRAD_RANK + r], pij);
-          pji = fma(ri[r], Lf[j * PIRL_GRAD_RANK + r], pji);
+          pij = fma(li[r], Rf[j * fsm + r * fsr], pij);
+          pji = fma(ri[r], Lf[j * fsm + r * fsr], pji);
         }
         const double lmj = lam[j];
         if (i == j) {
@@ -584,9 +810,8 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
         }
         cplx vj[PIRL_GRAD_NV / 2];   // (the staged copy is only 8-byte aligned: ff * ld is odd)
 #pragma unroll
-        for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vj[r] = make_double2(Vf[j * PIRL_GRAD_NV + 2 * r], Vf[j * PIRL_GRAD_NV + 2 * r + 1]);
-        cplx qj, Xj;
-        mode_qx(lmj, k0d, qj, Xj);
+        for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vj[r] = make_double2(Vf[j * vsm + 2 * r * vsr], Vf[j * vsm + (2 * r + 1) * vsr]);
+        const cplx qj = qS[j], Xj = XS[j];
         // S_f,ij = sum over pairs a_i conj(c_j) + a_j conj(c_i)
         cplx Sq = make_double2(0.0, 0.0);
 #pragma unroll
@@ -600,10 +825,17 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
         const cplx SXQ = cfma(vi[9], cconj(vj[8]), cmul(vj[9], cconj(vi[8])));
         // divided differences (f_j - f_i)/(lam_j - lam_i)
         const cplx dq = cinv(cadd(qi, qj));
-        cplx zz = make_double2(-k0d * (qj.x - qi.x), -k0d * (qj.y - qi.y));
-        cplx Xref = Xi;
-        if (zz.x > 0.0) { zz = make_double2(-zz.x, -zz.y); Xref = Xj; }
-        const cplx dX = cscale(cmul(cmul(Xref, cexpm1_over_z(zz)), dq), -k0d);
+        cplx dX;
+        const double dl = lmj - lmi;
+        if (fabs(dl) > 1e-2 * (fabs(lmi) + fabs(lmj))) {   // well separated: plain difference quotient (loses <= 2 digits)
+          const double idl = 1.0 / dl;
+          dX = make_double2((Xj.x - Xi.x) * idl, (Xj.y - Xi.y) * idl);
+        } else {                                            // close pair: X_ref (exp(z) - 1)/z with Re z <= 0
+          cplx zz = make_double2(-k0d * (qj.x - qi.x), -k0d * (qj.y - qi.y));
+          cplx Xref = Xi;
+          if (zz.x > 0.0) { zz = make_double2(-zz.x, -zz.y); Xref = Xj; }
+          dX = cscale(cmul(cmul(Xref, cexpm1_over_z(zz)), dq), -k0d);
+        }
         const cplx dD1 = cscale(cmul(cadd(Xi, Xj), dX), -1.0);
         const cplx dXQ = cfma(Xj, dq, cmul(qi, dX));
         cplx acc = cmul(cconj(Sq), dq);
@@ -616,6 +848,7 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
       }
     }
     __syncthreads();
+    RK_PHASE(24);
     cta_gemm<false>(M3, M0, M1, ff, ld);                 // W G_B
     __syncthreads();
     cta_gemm<true>(M1, M3, M0, ff, ld);                  // B-bar = W G_B W^T
@@ -624,29 +857,17 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     __syncthreads();
     cta_gemm<true>(M2, M3, M0, ff, ld);                  // A-bar = W G_A W^T
     __syncthreads();
+    RK_PHASE(25);
     for (int i = warp; i < ff; i += NW)
       for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, M2[i * ld + j], gAr, gAi);
-    // ---- M0 = E^-1 (recomputed: Gauss-Jordan without pivoting, E is SPD) ----
+    RK_PHASE(26);
+    // ---- M0 = E^-1, exported by the front kernel of this call (P.Einv) ----
     {
-      const double de = er - eg;
+      const double* Eg = P.Einv + (size_t)b * ff * ff;
       for (int i = warp; i < ff; i += NW)
-        for (int j = lane; j < ff; j += 32)
-          M0[i * ld + j] = fma(de, basis_toeplitz(i, j, N, cre, cim), (i == j) ? eg : 0.0);
+        for (int j = lane; j < ff; j += 32) M0[i * ld + j] = Eg[i * ff + j];
     }
-    for (int k = 0; k < ff; ++k) {
-      __syncthreads();
-      for (int t = tid; t < ff; t += NT) { rowk[t] = M0[k * ld + t]; colk[t] = M0[t * ld + k]; }
-      __syncthreads();
-      const double p = 1.0 / rowk[k];
-      for (int i = warp; i < ff; i += NW) {
-        const double f = colk[i] * p;
-        if (i == k) {
-          for (int j = lane; j < ff; j += 32) M0[i * ld + j] = (j == k) ? p : rowk[j] * p;
-        } else {
-          for (int j = lane; j < ff; j += 32) M0[i * ld + j] = (j == k) ? -f : fma(-f, rowk[j], M0[i * ld + j]);
-        }
-      }
-    }
+    RK_PHASE(27);
     // ---- M1 = (E^-1)-bar = S_K B-bar S_K^T  (2x2 cos/sin blocks swap and change sign; constant row / column drop out) ----
     for (int idx = tid; idx < N * N; idx += NT) {
       const int pp = idx / N, qq = idx - pp * N;
@@ -663,8 +884,10 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     __syncthreads();
     cta_gemm<false>(M1, M2, M0, ff, ld);                 // -E-bar = E^-1 (E^-1)-bar E^-1
     __syncthreads();
+    RK_PHASE(28);
     for (int i = warp; i < ff; i += NW)
       for (int j = lane; j < ff; j += 32) toeplitz_adjoint_add(i, j, N, -M1[i * ld + j], gEr, gEi);
+    RK_PHASE(29);
     __syncthreads();
     // ---- g_k = conj(c-bar_k) D_k ; pixel gradient = Re sum_k g_k exp(-2 pi i k p / n) ----
     for (int k = tid; k <= 2 * N; k += NT) {
@@ -683,5 +906,6 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
       const double ep = su[p] ? er : eg;
       G.grad[(size_t)b * nc + p] = 0.5 * (er - eg) * (vE - vA / (ep * ep));
     }
+    RK_PHASE(30);
   }
 }

@@ -45,6 +45,7 @@ struct KParams {
   double* scratch;            // per-CTA spill area for matrices that do not fit in shared memory
   size_t scratch_stride;      // doubles per CTA
   int smem_mats;              // how many (kernel-specific) matrices live in shared memory
+  double* Einv;               // optional [B][ff][ff]: E^-1 exported by the front kernels for the adjoint sweep (null otherwise)
   // outputs
   double* eff; double* de_r3; double* de_t3; int* status;
 };
@@ -230,6 +231,12 @@ __global__ void __launch_bounds__(NT) k_front(KParams P) {
       }
     }
     __syncthreads();
+    if (P.Einv) {
+      double* Eg = P.Einv + (size_t)b * ff * ff;
+      for (int i = warp; i < ff; i += NW)
+        for (int j = lane; j < ff; j += 32) Eg[i * ff + j] = E[i * ld + j];
+      __syncthreads();
+    }
     // ---- B = S_K^T E^-1 S_K - I, in place (2x2 cos/sin blocks swap and change sign) ----
     for (int idx = tid; idx < N * N; idx += NT) {
       int pp = idx / N, qq = idx - pp * N;

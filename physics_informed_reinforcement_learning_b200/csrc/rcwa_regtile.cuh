@@ -224,6 +224,13 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
       }
     }
     __syncthreads();
+    if (P.Einv && act) {   // adjoint sweep needs E^-1 (original harmonic order)
+      double* Eg = P.Einv + (size_t)sidx * FF * FF;
+#pragma unroll
+      for (int a = 0; a < RT; ++a)
+#pragma unroll
+        for (int b = 0; b < CT; ++b) Eg[(ti + TR * a) * FF + tj + TC * b] = t[a][b];
+    }
     // B'_ij = s_i s_j Einv_ij - delta_ij with s = (swapped) normalised kx: even slot -> -p sin(angle), odd slot -> +p sin(angle)
     {
       double si[RT], sj[CT];

@@ -7,8 +7,9 @@ from physics_informed_reinforcement_learning_b200 import RCWABatch
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 be = RCWABatch(256, 40, max_batch=B)
 pats = torch.from_numpy((np.random.default_rng(1234).integers(0, 2, (B, 256)) * 2 - 1).astype(np.int8)).cuda()
-be.evaluate(pats); torch.cuda.synchronize(); be.debug_fetch("phase_clk", 1)
-be.evaluate(pats); torch.cuda.synchronize()
+run = (lambda: be.evaluate_grad(pats)) if len(sys.argv) > 2 and sys.argv[2] == "grad" else (lambda: be.evaluate(pats))
+run(); torch.cuda.synchronize(); be.debug_fetch("phase_clk", 1)
+run(); torch.cuda.synchronize()
 c = be.debug_fetch("phase_clk", 1)
 tot = c.sum()
 for i, v in enumerate(c):
