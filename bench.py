@@ -252,8 +252,6 @@ def run_b200(args):
     eff_first = eff.clone()
 
     sampler = ClockSampler(local_rank)
-    be.set_stage_timing(True)
-    be.stage_times()
     l0 = be.launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
@@ -265,8 +263,20 @@ def run_b200(args):
         b.record()
     barrier()
     launches = be.launch_count() - l0
+    # per-kernel durations for the roofline: the same steps once more with the internal sub-chunk pipeline off, so that every
+    # kernel runs alone between its two events (in the pipelined timed region kernels of the two half-chunks overlap and a
+    # per-kernel duration is not defined); this is also how the ncu launch list in profiles/ sees them (serialised)
+    be.set_subchunk(0)
+    be.set_stage_timing(True)
+    be.stage_times()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        eff_serial = be.evaluate(d_pats, params=d_params)
+    torch.cuda.synchronize()
     stage = be.stage_times()
     be.set_stage_timing(False)
+    be.set_subchunk(-1)
+    assert torch.equal(eff_serial, eff), "pipelined and serial launch orders disagree"
     dev_s = sum(a.elapsed_time(b) for a, b in ev) * 1e-3
     job_s = max_over_ranks(dev_s, device=dev)
     assert torch.equal(eff, eff_first), "non-deterministic result"
@@ -354,7 +364,8 @@ def run_b200(args):
                 "share_of_step": ms / stage_total if stage_total else None,
                 "path": {"flops_per_eval": f_alg(ff), "achieved": value / world * f_alg(ff) / 1e12,
                          "frac": value / world * f_alg(ff) / 1e12 / fp64_peak},
-                "stages_ms_per_step": {k: v[0] / args.steps for k, v in stage.items()}}
+                "stages_ms_per_step": {k: v[0] / args.steps for k, v in stage.items()},
+                "stage_timing": "serial pass after the timed region (sub-chunk pipeline off): each kernel alone between two CUDA events"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": job_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",

@@ -96,6 +96,12 @@ int pirl_env_flip(int8_t* patterns, const int64_t* actions, int64_t B, int32_t n
 int pirl_env_reward(const double* eff_new, double* eff_prev, double* reward, double* best_eff,
                     int8_t* best_patterns, const int8_t* patterns, int64_t B, int32_t n_cells, void* stream);
 
+/* Tuning knob of the internal sub-chunk pipeline (k_ql of one half of a chunk runs under the front kernel of the other half):
+ * structures per sub-chunk; -1 = automatic (default: two halves for chunks of at least four waves), 0 = off (every kernel of
+ * a chunk runs alone on the caller's stream -- what bench.py uses to time single kernels for the roofline).  Results are
+ * bit-identical in every setting. */
+int pirl_rcwa_set_subchunk(pirl_handle* h, int32_t structures_per_subchunk);
+
 /* Number of kernels this library launched since the handle was created (bench.py's gpu_launches). */
 int64_t pirl_rcwa_launch_count(pirl_handle* h);
 

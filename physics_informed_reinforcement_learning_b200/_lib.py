@@ -10,7 +10,7 @@ SYMBOLS = [
     "pirl_abi_version", "pirl_last_error", "pirl_rcwa_create", "pirl_rcwa_destroy", "pirl_rcwa_eval",
     "pirl_rcwa_eval_host", "pirl_env_flip", "pirl_env_reward", "pirl_rcwa_launch_count", "pirl_rcwa_debug_fetch",
     "pirl_rcwa_num_stages", "pirl_rcwa_stage_name", "pirl_rcwa_set_stage_timing", "pirl_rcwa_stage_times",
-    "pirl_rcwa_eval_grad", "pirl_rcwa_eval_grad_host",
+    "pirl_rcwa_eval_grad", "pirl_rcwa_eval_grad_host", "pirl_rcwa_set_subchunk",
 ]
 
 
@@ -53,6 +53,8 @@ def load():
     lib.pirl_rcwa_stage_name.argtypes = [i32]
     lib.pirl_rcwa_stage_name.restype = C.c_char_p
     lib.pirl_rcwa_set_stage_timing.argtypes = [vp, i32]
+    lib.pirl_rcwa_set_subchunk.argtypes = [vp, i32]
+    lib.pirl_rcwa_set_subchunk.restype = C.c_int
     lib.pirl_rcwa_stage_times.argtypes = [vp, dp, dp]
     for name in ("pirl_rcwa_create", "pirl_rcwa_destroy", "pirl_rcwa_eval", "pirl_rcwa_eval_host", "pirl_env_flip",
                  "pirl_env_reward", "pirl_rcwa_debug_fetch", "pirl_rcwa_set_stage_timing", "pirl_rcwa_stage_times", "pirl_rcwa_eval_grad",

@@ -45,6 +45,10 @@ struct pirl_handle {
   // sub-chunk pipeline: the latency-bound QL kernel of sub-chunk c runs on a side stream under the front kernels of c+1...
   static constexpr int kMaxSub = 16, kSide = 4;
   cudaStream_t side[kSide] = {nullptr, nullptr, nullptr, nullptr};
+  cudaStream_t fstream[kSide] = {nullptr, nullptr, nullptr, nullptr};   // front kernels of the sub-chunks
+  cudaEvent_t evStart = nullptr;
+  int* queues = nullptr; unsigned qslot = 0;      // work counters of the persistent kernels (one per launch, round robin)
+  static constexpr int kQueues = 64;
   cudaEvent_t evF[kMaxSub] = {}, evQ[kMaxSub] = {};
   int sub_size = 0;
   double* scratch = nullptr;
@@ -84,7 +88,9 @@ static constexpr int kNumStages = 9;
 #ifdef PIRL_FRONT_9x9
 using Cfg81 = TileCfg<81, 9, 9, 9, 9, 3>;
 #else
-using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2>;
+// rk_front is capped at 112 registers: 4 warps x 112 + one k_ql warp x 64 registers fill one SM sub-partition exactly, so a
+// k_ql CTA can sit beside two rk_front CTAs (sub-chunk pipeline); ptxas reports no spills at this cap
+using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2, 112>;
 #endif
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
 using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real tile at a time, two CTAs per SM
@@ -277,19 +283,22 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   h->scratch_ctas = std::max(std::max(h->front_grid, h->tri_grid), h->tail_grid);
   h->scratch_stride = 2 * m2 + 2 * (2 * (size_t)ff * h->ld) + 16;
   CUDA_TRY(dmalloc(&h->scratch, (size_t)h->scratch_ctas * h->scratch_stride));
+  CUDA_TRY(dmalloc(&h->queues, pirl_handle::kQueues));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
   {
     int lo = 0, hi = 0;
     CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     for (int i = 0; i < pirl_handle::kSide; ++i) CUDA_TRY(cudaStreamCreateWithPriority(&h->side[i], cudaStreamNonBlocking, hi));
+    for (int i = 0; i < pirl_handle::kSide; ++i) CUDA_TRY(cudaStreamCreateWithPriority(&h->fstream[i], cudaStreamNonBlocking, lo));
+    CUDA_TRY(cudaEventCreateWithFlags(&h->evStart, cudaEventDisableTiming));
     for (int i = 0; i < pirl_handle::kMaxSub; ++i) {
       CUDA_TRY(cudaEventCreateWithFlags(&h->evF[i], cudaEventDisableTiming));
       CUDA_TRY(cudaEventCreateWithFlags(&h->evQ[i], cudaEventDisableTiming));
     }
-    // sub-chunk pipeline: off by default (PIRL_SUBCHUNK=<structures per sub-chunk> enables it).  Measured with the CTA trace
-    // (tools/cta_trace.py, profiles/r01h_cta_trace_subchunk592.txt): persistent front / tail grids sized to the whole machine
-    // leave straggler waves when k_ql CTAs hold SM slots, so the overlap loses more than it hides.
-    h->sub_size = 0;
+    // sub-chunk pipeline (register-tile path): a chunk of at least 4 full waves is cut in two halves by default
+    // (PIRL_SUBCHUNK=<structures per sub-chunk> overrides, 0 switches it off).  Measured with the CTA trace
+    // (tools/cta_trace.py, profiles/r01p_cta_trace_subchunk2048.txt): 8.72 -> 8.23 ms per 4096.
+    h->sub_size = -1;   // auto
     if (const char* e = getenv("PIRL_SUBCHUNK")) h->sub_size = atoi(e);
     h->no_rktail = getenv("PIRL_NO_RKTAIL") != nullptr;
   }
@@ -302,11 +311,13 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaSetDevice(h->cfg.device);
   cudaFree(h->d_tw); cudaFree(h->d_Dk);
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
-  cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace);
+  cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace); cudaFree(h->queues);
   cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
   cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_Vf); cudaFree(h->g_Einv); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
+  for (auto q : h->fstream) if (q) cudaStreamDestroy(q);
+  if (h->evStart) cudaEventDestroy(h->evStart);
   for (auto e : h->evF) if (e) cudaEventDestroy(e);
   for (auto e : h->evQ) if (e) cudaEventDestroy(e);
   for (auto& p : h->ev_pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
@@ -333,8 +344,15 @@ static KParams sub_params(const KParams& P0, int n_cells, int ff, int off, int c
   return P;
 }
 
+static int* next_queue(pirl_handle* h, cudaStream_t st) {
+  int* q = h->queues + (h->qslot++ % pirl_handle::kQueues);
+  cudaMemsetAsync(q, 0, sizeof(int), st);
+  return q;
+}
+
 static void launch_front(pirl_handle* h, KParams P, cudaStream_t st) {
   if (h->regtile) {
+    if (P.B > h->rk_front_grid) P.queue = next_queue(h, st);
     StageTimer t(h, 5, st);
     rk_front<Cfg81><<<std::min(P.B, h->rk_front_grid), Cfg81::NT, h->rk_front_smem, st>>>(P);
     h->launches += 1;
@@ -362,13 +380,14 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
     h->launches += 1;
 }
 
-static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
-  launch_apply(h, P, st);
+static void launch_tail(pirl_handle* h, KParams P, cudaStream_t st) {
   if (h->regtile && !h->no_rktail) {
+    if (!h->old_rktail && P.B > h->rk_tail2_grid) P.queue = next_queue(h, st);
     StageTimer t(h, 6, st);
     if (h->old_rktail) rk_tail<Cfg81T, kTailMmax><<<std::min(P.B, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
     else RK_TAIL2<<<std::min(P.B, h->rk_tail2_grid), Cfg81T2::NT, h->rk_tail2_smem, st>>>(P);
     P.fallback_only = 1;
+    P.queue = nullptr;
     h->launches += 1;
   }
   P.smem_mats = h->tail_mats;
@@ -378,6 +397,11 @@ static void launch_back(pirl_handle* h, KParams P, cudaStream_t st) {
   else if (h->ff <= 128) k_tail<TAIL_NT, 4><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
   else k_tail<TAIL_NT, 8><<<tg, TAIL_NT, h->tail_smem, st>>>(P);
   h->launches += 1;
+}
+
+static void launch_back(pirl_handle* h, const KParams& P, cudaStream_t st) {
+  launch_apply(h, P, st);
+  launch_tail(h, P, st);
 }
 
 static KParams chunk_params(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
@@ -403,7 +427,8 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   // chunk is cut into sub-chunks: all front kernels are issued first on the caller's stream, each sub-chunk's k_ql runs on
   // a high-priority side stream as soon as its front kernel is done (under the following front / back kernels), and the
   // back kernels (k_apply, tail) follow on the caller's stream, each waiting for its own k_ql.
-  const int sub = h->sub_size;
+  int sub = h->sub_size;
+  if (sub < 0) sub = (h->regtile && Bc >= 4 * h->rk_front_grid) ? (Bc + 1) / 2 : 0;
   int nsub = (sub > 0) ? (Bc + sub - 1) / sub : 1;
   if (nsub > pirl_handle::kMaxSub) nsub = pirl_handle::kMaxSub;
   if (nsub <= 1) {
@@ -411,28 +436,47 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
     launch_ql(h, P, st);
     launch_back(h, P, st);
   } else {
+    // Order on the device: fronts of all sub-chunks back to back (each on its own stream so that the persistent CTAs of
+    // sub-chunk c+1 backfill the SMs as those of c drain), k_ql(c) on a high-priority side stream as soon as front(c) is done
+    // (one warp per SM, co-resident with two rk_front CTAs: that is why rk_front is capped at 112 registers -- 4 warps x 112
+    // + one k_ql warp x 64 registers fill one SM sub-partition exactly), then all k_apply, then all tails on the caller's
+    // stream: the last k_ql hides under the k_apply launches of the earlier sub-chunks.
     const int per = (sub * nsub >= Bc) ? sub : (Bc + nsub - 1) / nsub;
     KParams Ps[pirl_handle::kMaxSub];
+    CUDA_TRY(cudaEventRecord(h->evStart, st));
     for (int c = 0; c < nsub; ++c) {
       const int off = c * per, cnt = std::min(per, Bc - off);
       Ps[c] = sub_params(P, h->cfg.n_cells, h->ff, off, cnt);
-      launch_front(h, Ps[c], st);
-      CUDA_TRY(cudaEventRecord(h->evF[c], st));
+      cudaStream_t fs = h->regtile ? h->fstream[c % pirl_handle::kSide] : h->fstream[0];   // the shared-memory front kernels share per-CTA scratch
+      if (c < pirl_handle::kSide) CUDA_TRY(cudaStreamWaitEvent(fs, h->evStart, 0));
+      launch_front(h, Ps[c], fs);
+      CUDA_TRY(cudaEventRecord(h->evF[c], fs));
       cudaStream_t qs = h->side[c % pirl_handle::kSide];
       CUDA_TRY(cudaStreamWaitEvent(qs, h->evF[c], 0));
       launch_ql(h, Ps[c], qs);
       CUDA_TRY(cudaEventRecord(h->evQ[c], qs));
     }
-    for (int c = 0; c < nsub; ++c) {
+    // caller's stream: k_apply of all but the last sub-chunk, ONE tail launch over them (the last k_ql hides under it; the
+    // tail CTAs it displaces fetch less work), then k_apply + tail of the last sub-chunk
+    for (int c = 0; c + 1 < nsub; ++c) {
       CUDA_TRY(cudaStreamWaitEvent(st, h->evQ[c], 0));
-      launch_back(h, Ps[c], st);
+      launch_apply(h, Ps[c], st);
     }
+    launch_tail(h, sub_params(P, h->cfg.n_cells, h->ff, 0, (nsub - 1) * per), st);
+    CUDA_TRY(cudaStreamWaitEvent(st, h->evQ[nsub - 1], 0));
+    launch_apply(h, Ps[nsub - 1], st);
+    launch_tail(h, Ps[nsub - 1], st);
   }
   h->last_chunk = Bc;
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
+extern "C" int pirl_rcwa_set_subchunk(pirl_handle* h, int32_t structures_per_subchunk) {
+  if (!h) return fail(-1, "null argument");
+  h->sub_size = structures_per_subchunk;
+  return 0;
+}
 extern "C" int pirl_rcwa_num_stages(void) { return kNumStages; }
 extern "C" const char* pirl_rcwa_stage_name(int32_t s) { return (s >= 0 && s < kNumStages) ? kStageNames[s] : ""; }
 extern "C" int pirl_rcwa_set_stage_timing(pirl_handle* h, int32_t enable) {

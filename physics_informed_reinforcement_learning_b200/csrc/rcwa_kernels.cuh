@@ -45,6 +45,7 @@ struct KParams {
   double* scratch;            // per-CTA spill area for matrices that do not fit in shared memory
   size_t scratch_stride;      // doubles per CTA
   int smem_mats;              // how many (kernel-specific) matrices live in shared memory
+  int* queue;                 // optional work counter (zeroed before the launch): persistent CTAs fetch structures dynamically
   double* Einv;               // optional [B][ff][ff]: E^-1 exported by the front kernels for the adjoint sweep (null otherwise)
   // outputs
   double* eff; double* de_r3; double* de_t3; int* status;
@@ -101,6 +102,17 @@ struct CtaTrace {
     r[3] = pirl_gtime();
   }
 };
+
+// next structure of a persistent CTA: static grid stride without a queue, else first item = blockIdx.x, then
+// gridDim.x + atomicAdd(queue, 1).  Dynamic fetching keeps late-starting CTAs (SM slots held by a co-running kernel) from
+// becoming stragglers.  Must be reached by every thread of the CTA.
+__device__ __forceinline__ int pirl_next_item(int* queue, int cur, int* slot) {
+  if (!queue) return cur + (int)gridDim.x;
+  __syncthreads();
+  if (threadIdx.x == 0) *slot = (int)gridDim.x + atomicAdd(queue, 1);
+  __syncthreads();
+  return *slot;
+}
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

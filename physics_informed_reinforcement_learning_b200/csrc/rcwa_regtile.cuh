@@ -16,14 +16,14 @@
 #pragma once
 #include "rcwa_kernels.cuh"
 
-template <int FF_, int TR_, int TC_, int RT_, int CT_, int MINB_>
+template <int FF_, int TR_, int TC_, int RT_, int CT_, int MINB_, int REGCAP_ = 255>
 struct TileCfg {
   static constexpr int FF = FF_, TR = TR_, TC = TC_, RT = RT_, CT = CT_, MINB = MINB_;
   static constexpr int N = (FF - 1) / 2;
   static constexpr int NTHR = TR * TC;
   static constexpr int NT = ((NTHR + 31) / 32) * 32;
   // register cap for MINB CTAs per SM
-  static constexpr int MAXREG = ((65536 / (MINB * NT)) / 8) * 8;
+  static constexpr int MAXREG = REGCAP_ < ((65536 / (MINB * NT)) / 8) * 8 ? REGCAP_ : ((65536 / (MINB * NT)) / 8) * 8;
   static constexpr int LD = (FF % 2) ? FF : FF + 1;   // odd leading dimension: conflict-free column walks
   static constexpr int KA_PER_KB = TR / TC;           // tile-row block index = kb / KA_PER_KB
   static_assert(TR * RT == FF && TC * CT == FF, "exact tiling only");
@@ -87,11 +87,12 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
   const int ti = act ? tid / TC : TR - 1;
   const int tj = act ? tid % TC : TC - 1;
   __shared__ int sbad;
+  __shared__ int snext;
   const CtaTrace trc(P.trace);
 
   for (int t = tid; t < nc; t += NT) twS[t] = P.tw[t];
 
-  for (int sidx = blockIdx.x; sidx < P.B; sidx += gridDim.x) {
+  for (int sidx = blockIdx.x; sidx < P.B; sidx = pirl_next_item(P.queue, sidx, &snext)) {
     __syncthreads();
     if (tid == 0) sbad = 0;
     const double* pr = P.params + (size_t)sidx * P.pstride;

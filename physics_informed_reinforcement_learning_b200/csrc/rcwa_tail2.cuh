@@ -240,8 +240,9 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
   const int ti = act ? tid / TC : TR - 1;
   const int tj = act ? tid % TC : TC - 1;
   const CtaTrace trc(P.trace);
+  __shared__ int snext;
 
-  for (int sidx = blockIdx.x; sidx < P.B; sidx += gridDim.x) {
+  for (int sidx = blockIdx.x; sidx < P.B; sidx = pirl_next_item(P.queue, sidx, &snext)) {
     __syncthreads();
     long long pc_ = clock64();
     const double* pr = P.params + (size_t)sidx * P.pstride;

@@ -189,6 +189,10 @@ class RCWABatch:
         """Bracket every kernel of ``evaluate`` with CUDA events on the launching stream (bench.py's roofline)."""
         _lib.check(self.lib.pirl_rcwa_set_stage_timing(self._h, 1 if enable else 0))
 
+    def set_subchunk(self, structures_per_subchunk: int):
+        """-1 automatic, 0 off, n > 0 structures per sub-chunk of the internal pipeline (``pirl_rcwa_set_subchunk``)."""
+        _lib.check(self.lib.pirl_rcwa_set_subchunk(self._h, int(structures_per_subchunk)))
+
     def stage_times(self):
         """{kernel name: (total ms, launches)} since the last call; synchronises the recorded events."""
         n = self.lib.pirl_rcwa_num_stages()
