@@ -90,7 +90,11 @@ using Cfg81 = TileCfg<81, 9, 9, 9, 9, 3>;
 #else
 // rk_front is capped at 112 registers: 4 warps x 112 + one k_ql warp x 64 registers fill one SM sub-partition exactly, so a
 // k_ql CTA can sit beside two rk_front CTAs (sub-chunk pipeline); ptxas reports no spills at this cap
+#ifdef PIRL_FRONT3
+using Cfg81 = TileCfg<81, 27, 9, 3, 9, 3, 80>;    // experiment: three CTAs per SM (spills)
+#else
 using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2, 112>;
+#endif
 #endif
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
 using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real tile at a time, two CTAs per SM
