@@ -63,6 +63,7 @@ struct pirl_handle {
   unsigned long long* phase_clk = nullptr;   // [32] device counters (PIRL_PHASE_CLOCKS=1)
   unsigned long long* trace = nullptr;       // CTA trace records (PIRL_TRACE=1)
   bool no_rktail = false, old_rktail = false; int rk_tail2_grid = 0; size_t rk_tail2_smem = 0;
+  bool regfront121 = false;   // ff = 121: padded register-tile front kernel, shared-memory kernels behind it
   bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
@@ -96,6 +97,8 @@ using Cfg81 = TileCfg<81, 27, 9, 3, 9, 3, 80>;    // experiment: three CTAs per 
 using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2, 112>;
 #endif
 #endif
+// order 60: 121 = 11^2 has no usable exact tiling -> 126 = 42 x 3 = 14 x 9 with five identity-padded rows / columns
+using Cfg121 = TileCfg<126, 42, 14, 3, 9, 1, 96, 121>;   // 19 warps: 5 on one SM sub-partition -> at most 102 registers each
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
 using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real tile at a time, two CTAs per SM
 #define RK_TAIL2 rk_tail2<Cfg81T2, 56, 10, 5>
@@ -271,6 +274,16 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->rk_tail2_grid = h->sm_count * per_sm;
     h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }
+  if (ff == Cfg121::FFR && !getenv("PIRL_NO_REGTILE")) {
+    h->regfront121 = true;
+    h->rk_front_smem = (size_t)FrontSmem<Cfg121>::doubles(nc) * 8;
+    CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg121>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    CUDA_TRY(max_carveout(rk_front<Cfg121>));
+    int per_sm = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_front<Cfg121>, Cfg121::NT, h->rk_front_smem));
+    if (per_sm < 1) return fail(-9, "rk_front (order 60) does not fit on this device");
+    h->rk_front_grid = h->sm_count * per_sm;
+  }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
   CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
@@ -355,7 +368,12 @@ static int* next_queue(pirl_handle* h, cudaStream_t st) {
 }
 
 static void launch_front(pirl_handle* h, KParams P, cudaStream_t st) {
-  if (h->regtile) {
+  if (h->regfront121) {
+    if (P.B > h->rk_front_grid) P.queue = next_queue(h, st);
+    StageTimer t(h, 5, st);
+    rk_front<Cfg121><<<std::min(P.B, h->rk_front_grid), Cfg121::NT, h->rk_front_smem, st>>>(P);
+    h->launches += 1;
+  } else if (h->regtile) {
     if (P.B > h->rk_front_grid) P.queue = next_queue(h, st);
     StageTimer t(h, 5, st);
     rk_front<Cfg81><<<std::min(P.B, h->rk_front_grid), Cfg81::NT, h->rk_front_smem, st>>>(P);

@@ -16,10 +16,13 @@
 #pragma once
 #include "rcwa_kernels.cuh"
 
-template <int FF_, int TR_, int TC_, int RT_, int CT_, int MINB_, int REGCAP_ = 255>
+// FFR_ (0 = FF_): number of REAL harmonics when the tile grid is padded (rk_front only): rows / columns >= FFR are identity
+// padding that stays decoupled through every factorisation step and is dropped at the stores (e.g. 121 = 11^2 -> 126 = 42x3 = 14x9).
+template <int FF_, int TR_, int TC_, int RT_, int CT_, int MINB_, int REGCAP_ = 255, int FFR_ = 0>
 struct TileCfg {
   static constexpr int FF = FF_, TR = TR_, TC = TC_, RT = RT_, CT = CT_, MINB = MINB_;
-  static constexpr int N = (FF - 1) / 2;
+  static constexpr int FFR = FFR_ > 0 ? FFR_ : FF_;
+  static constexpr int N = (FFR - 1) / 2;
   static constexpr int NTHR = TR * TC;
   static constexpr int NT = ((NTHR + 31) / 32) * 32;
   // register cap for MINB CTAs per SM
@@ -62,6 +65,8 @@ struct FrontSmem {
 template <class C>
 __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
   constexpr int FF = C::FF, TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, N = C::N, LD = C::LD, NT = C::NT;
+  constexpr int FFR = C::FFR;            // real harmonics (== FF unless the tile grid is padded)
+  constexpr bool PAD = FFR != FF;
   constexpr int z = 2 * N;
   using S = FrontSmem<C>;
   extern __shared__ __align__(16) double sm[];
@@ -128,7 +133,8 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
         for (int b = 0; b < CT; ++b) {
           const int i = ti + TR * a, j = tj + TC * b;
           const int pi = (i < z) ? (i ^ 1) : i, pj = (j < z) ? (j ^ 1) : j;
-          t[a][b] = fma(da, basis_toeplitz(pi, pj, N, cre, cim), (i == j) ? ia : 0.0);
+          if (PAD && (i >= FFR || j >= FFR)) t[a][b] = (i == j) ? 1.0 : 0.0;
+          else t[a][b] = fma(da, basis_toeplitz(pi, pj, N, cre, cim), (i == j) ? ia : 0.0);
         }
     }
 #pragma unroll
@@ -181,7 +187,8 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
 #pragma unroll
         for (int b = 0; b < CT; ++b) {
           const int i = ti + TR * a, j = tj + TC * b;
-          t[a][b] = fma(de, basis_toeplitz(i, j, N, cre, cim), (i == j) ? eg : 0.0);
+          if (PAD && (i >= FFR || j >= FFR)) t[a][b] = (i == j) ? 1.0 : 0.0;
+          else t[a][b] = fma(de, basis_toeplitz(i, j, N, cre, cim), (i == j) ? eg : 0.0);
         }
     }
 #pragma unroll
@@ -226,11 +233,12 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
     }
     __syncthreads();
     if (P.Einv && act) {   // adjoint sweep needs E^-1 (original harmonic order)
-      double* Eg = P.Einv + (size_t)sidx * FF * FF;
+      double* Eg = P.Einv + (size_t)sidx * FFR * FFR;
 #pragma unroll
       for (int a = 0; a < RT; ++a)
 #pragma unroll
-        for (int b = 0; b < CT; ++b) Eg[(ti + TR * a) * FF + tj + TC * b] = t[a][b];
+        for (int b = 0; b < CT; ++b)
+          if (!PAD || (ti + TR * a < FFR && tj + TC * b < FFR)) Eg[(ti + TR * a) * FFR + tj + TC * b] = t[a][b];
     }
     // B'_ij = s_i s_j Einv_ij - delta_ij with s = (swapped) normalised kx: even slot -> -p sin(angle), odd slot -> +p sin(angle)
     {
@@ -489,19 +497,20 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
     RK_PHASE(6);
     // ---- store: t(i, j) = M0'[j][i] (swapped ordering);  old layout Wbuf[row][mode] in ORIGINAL harmonic order ----
     if (act) {
-      double* Wg = P.Wbuf + (size_t)sidx * FF * FF;
+      double* Wg = P.Wbuf + (size_t)sidx * FFR * FFR;
 #pragma unroll
       for (int b = 0; b < CT; ++b) {
         const int j = tj + TC * b;
         const int row = (j < z) ? (j ^ 1) : j;
 #pragma unroll
-        for (int a = 0; a < RT; ++a) Wg[row * FF + ti + TR * a] = t[a][b];
+        for (int a = 0; a < RT; ++a)
+          if (!PAD || (j < FFR && ti + TR * a < FFR)) Wg[row * FFR + ti + TR * a] = t[a][b];
       }
     }
     if (bad) sbad = 1;
     __syncthreads();
-    double* tg = P.tri + (size_t)sidx * 2 * FF;
-    for (int q = tid; q < FF; q += NT) { tg[q] = dd[q]; tg[FF + q] = ee[q]; }
+    double* tg = P.tri + (size_t)sidx * 2 * FFR;
+    for (int q = tid; q < FFR; q += NT) { tg[q] = dd[q]; tg[FFR + q] = (q == FFR - 1) ? 0.0 : ee[q]; }
     if (tid == 0) P.wstatus[sidx] = sbad ? PIRL_ST_NPD : 0;
     RK_PHASE(7);
   }
