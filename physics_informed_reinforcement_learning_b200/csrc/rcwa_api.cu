@@ -99,6 +99,8 @@ using Cfg81 = TileCfg<81, 27, 9, 3, 9, 2, 112>;
 #endif
 // order 60: 121 = 11^2 has no usable exact tiling -> 126 = 42 x 3 = 14 x 9 with five identity-padded rows / columns
 using Cfg121 = TileCfg<126, 42, 14, 3, 9, 1, 96, 121>;   // 19 warps: 5 on one SM sub-partition -> at most 102 registers each
+#define RK_TAIL2_121 rk_tail2<Cfg121, 64, 10, 5>
+using Tail2Sm121 = Tail2Smem<Cfg121, 64, 10, 5>;   // one CTA per SM: room for 64 significant evanescent modes
 using Cfg81T = TileCfg<81, 27, 9, 3, 9, 1>;   // tail: complex tiles, one CTA per SM
 using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real tile at a time, two CTAs per SM
 #define RK_TAIL2 rk_tail2<Cfg81T2, 56, 10, 5>
@@ -283,6 +285,12 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rk_front<Cfg121>, Cfg121::NT, h->rk_front_smem));
     if (per_sm < 1) return fail(-9, "rk_front (order 60) does not fit on this device");
     h->rk_front_grid = h->sm_count * per_sm;
+    h->rk_tail2_smem = (size_t)Tail2Sm121::doubles * 8;
+    CUDA_TRY(cudaFuncSetAttribute(RK_TAIL2_121, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
+    CUDA_TRY(max_carveout(RK_TAIL2_121));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, RK_TAIL2_121, Cfg121::NT, h->rk_tail2_smem));
+    if (per_sm < 1) return fail(-9, "rk_tail2 (order 60) does not fit on this device");
+    h->rk_tail2_grid = h->sm_count * per_sm;
   }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
   CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
@@ -403,7 +411,14 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
 }
 
 static void launch_tail(pirl_handle* h, KParams P, cudaStream_t st) {
-  if (h->regtile && !h->no_rktail) {
+  if (h->regfront121 && !h->no_rktail) {
+    if (P.B > h->rk_tail2_grid) P.queue = next_queue(h, st);
+    StageTimer t(h, 6, st);
+    RK_TAIL2_121<<<std::min(P.B, h->rk_tail2_grid), Cfg121::NT, h->rk_tail2_smem, st>>>(P);
+    P.fallback_only = 1;
+    P.queue = nullptr;
+    h->launches += 1;
+  } else if (h->regtile && !h->no_rktail) {
     if (!h->old_rktail && P.B > h->rk_tail2_grid) P.queue = next_queue(h, st);
     StageTimer t(h, 6, st);
     if (h->old_rktail) rk_tail<Cfg81T, kTailMmax><<<std::min(P.B, h->rk_tail_grid), Cfg81T::NT, h->rk_tail_smem, st>>>(P);
@@ -613,6 +628,12 @@ extern "C" int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, 
     case 4: {
       std::vector<int> tmp(B);
       CUDA_TRY(cudaMemcpy(tmp.data(), h->nrot, B * sizeof(int), cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < B && (int64_t)i < max_elems; ++i) dst[i] = (double)tmp[i];
+      return 0;
+    }
+    case 7: {   // working status words of the last chunk (bit 0x100: layer solve left to the generic kernel)
+      std::vector<int> tmp(B);
+      CUDA_TRY(cudaMemcpy(tmp.data(), h->wstatus, B * sizeof(int), cudaMemcpyDeviceToHost));
       for (size_t i = 0; i < B && (int64_t)i < max_elems; ++i) dst[i] = (double)tmp[i];
       return 0;
     }

@@ -207,6 +207,8 @@ __device__ __forceinline__ void t2_product(double (&t)[C::RT][C::CT], const doub
 template <class C, int NSMAX, int NPMAX, int NHMAX>
 __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
   constexpr int FF = C::FF, TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, N = C::N, LD = C::LD, NT = C::NT;
+  constexpr int FFR = C::FFR;            // real modes / harmonics; the FF - FFR padded ones are decoupled, strongly evanescent dummies
+  constexpr bool PAD = FFR != FF;
   constexpr int z = 2 * N;
   using S = Tail2Smem<C, NSMAX, NPMAX, NHMAX>;
   constexpr int FE = S::FE, NXB = S::NXB, NCT = S::NCT, NCB = S::NCB, NPX = NPMAX + NHMAX;
@@ -250,9 +252,9 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
     const double sa = sin(pr[1] * (3.14159265358979323846 / 180.0));
     const double k0d = 2.0 * 3.14159265358979323846 / wl * thick;
     const double nI = P.n_inc, nII = P.n_exit;
-    const double* lamg = P.lam + (size_t)sidx * FF;
-    const double* Wg = P.Wbuf + (size_t)sidx * FF * FF;
-    for (int t = tid; t < FF; t += NT) lamS[t] = lamg[t];
+    const double* lamg = P.lam + (size_t)sidx * FFR;
+    const double* Wg = P.Wbuf + (size_t)sidx * FFR * FFR;
+    for (int t = tid; t < FF; t += NT) lamS[t] = (!PAD || t < FFR) ? lamg[t] : 1e12;   // padded modes: q = 1e6, X = 0
     if (tid < 8) cnt[tid] = 0;
     __syncthreads();
     // ---- sort modes by descending eigenvalue (rank by counting); slab scalars; external-medium diagonals ----
@@ -274,8 +276,9 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
       }
       Cd[rk] = cdv; Sg[rk] = sgv;
       // harmonic tid (original order: 2(p-1) cos_p, 2(p-1)+1 sin_p, 2N const)
+      const bool padh = PAD && tid >= FFR;      // padded harmonic: no admittance, not a propagating order
       const double kap = (tid < z) ? ((tid >> 1) + 1) * sa : 0.0;
-      const double aI = nI * nI - kap * kap, aII = nII * nII - kap * kap;
+      const double aI = padh ? 0.0 : nI * nI - kap * kap, aII = padh ? 0.0 : nII * nII - kap * kap;
       dre[tid] = (aI < 0.0) ? sqrt(-aI) / (nI * nI) : 0.0;
       dre[FE + tid] = (aII < 0.0) ? sqrt(-aII) / (nII * nII) : 0.0;
       if (aI > 0.0 || aII > 0.0) {       // propagating harmonic: its slot in the border lists (ordered by index)
@@ -306,7 +309,8 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
     // ---- W -> shared, columns permuted into sorted order ----
     for (int idx = tid; idx < FF * FF; idx += NT) {
       const int r = idx / FF, j = idx - r * FF;
-      Wsm[r * LD + pos[j]] = Wg[idx];
+      if (!PAD) Wsm[r * LD + pos[j]] = Wg[idx];
+      else Wsm[r * LD + pos[j]] = (r < FFR && j < FFR) ? Wg[r * FFR + j] : 0.0;
     }
     __syncthreads();
     RK_PHASE(8);

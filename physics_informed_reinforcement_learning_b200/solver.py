@@ -204,7 +204,7 @@ class RCWABatch:
     def debug_fetch(self, what: str, B: int):
         ff = self.ff
         code, shape = {"C": (0, (B, ff, ff)), "tri": (1, (B, 2, ff)), "lam": (2, (B, ff)),
-                       "W": (3, (B, ff, ff)), "nrot": (4, (B,)), "phase_clk": (5, (32,)), "trace": (6, (0,))}[what]
+                       "W": (3, (B, ff, ff)), "nrot": (4, (B,)), "wstatus": (7, (B,)), "phase_clk": (5, (32,)), "trace": (6, (0,))}[what]
         if what == "trace":
             raw = np.zeros(1 + 4 * (1 << 20), dtype=np.uint64)
             _lib.check(self.lib.pirl_rcwa_debug_fetch(self._h, 6, raw.ctypes.data, raw.size))
