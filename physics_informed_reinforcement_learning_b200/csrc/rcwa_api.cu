@@ -465,7 +465,7 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   // a high-priority side stream as soon as its front kernel is done (under the following front / back kernels), and the
   // back kernels (k_apply, tail) follow on the caller's stream, each waiting for its own k_ql.
   int sub = h->sub_size;
-  if (sub < 0) sub = (h->regtile && Bc >= 4 * h->rk_front_grid) ? (Bc + 1) / 2 : 0;
+  if (sub < 0) sub = ((h->regtile || h->regfront121) && Bc >= 4 * h->rk_front_grid) ? (Bc + 1) / 2 : 0;
   int nsub = (sub > 0) ? (Bc + sub - 1) / sub : 1;
   if (nsub > pirl_handle::kMaxSub) nsub = pirl_handle::kMaxSub;
   if (nsub <= 1) {
@@ -484,7 +484,7 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
     for (int c = 0; c < nsub; ++c) {
       const int off = c * per, cnt = std::min(per, Bc - off);
       Ps[c] = sub_params(P, h->cfg.n_cells, h->ff, off, cnt);
-      cudaStream_t fs = h->regtile ? h->fstream[c % pirl_handle::kSide] : h->fstream[0];   // the shared-memory front kernels share per-CTA scratch
+      cudaStream_t fs = (h->regtile || h->regfront121) ? h->fstream[c % pirl_handle::kSide] : h->fstream[0];   // the shared-memory front kernels share per-CTA scratch
       if (c < pirl_handle::kSide) CUDA_TRY(cudaStreamWaitEvent(fs, h->evStart, 0));
       launch_front(h, Ps[c], fs);
       CUDA_TRY(cudaEventRecord(h->evF[c], fs));

@@ -5,8 +5,9 @@ import numpy as np, torch
 sys.path.insert(0, ".")
 from physics_informed_reinforcement_learning_b200 import RCWABatch
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+ORDER = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 big = torch.from_numpy(np.random.default_rng(1234).integers(0, 2, (B, 256)).astype(np.int8) * 2 - 1).cuda()
-be = RCWABatch(256, 40, max_batch=B, device=0)
+be = RCWABatch(256, ORDER, max_batch=B, device=0)
 for _ in range(2): be.evaluate_grad(big)
 torch.cuda.synchronize()
 be.set_stage_timing(True); be.stage_times()
