@@ -296,3 +296,36 @@ def test_stage_timers_and_launch_counter(pkg, torch_mod):
     assert launched == sum(c for _, c in times.values()) > 0
     assert all(ms > 0 for ms, c in times.values() if c)
     be.close()
+
+
+def test_register_tile_paths_against_shared_memory_kernels_and_pipeline_settings(pkg, torch_mod):
+    """Orders 40 and 60 run register-tile kernels (order 60 on a padded 126-tile grid) and, for large chunks, the sub-chunk
+    pipeline.  The generic shared-memory kernels (PIRL_NO_REGTILE=1) are an independent implementation of the same path: both
+    must agree far below the parity tolerance, and the launch order (pipeline on / off / other split) must not change a bit."""
+    torch = torch_mod
+    rng = np.random.default_rng(77)
+    for order, count in ((40, 1300), (60, 700)):
+        pats = (rng.integers(0, 2, (count, 256)) * 2 - 1).astype(np.int8)
+        pats[:64] = np.repeat(rng.integers(0, 2, (64, 16)) * 2 - 1, 16, axis=1)
+        d = torch.from_numpy(pats).cuda()
+        be = pkg.RCWABatch(256, order, max_batch=count, device=0)
+        e_auto, r3, t3, st = be.evaluate(d, return_orders=True)
+        be.set_subchunk(0)
+        e_off = be.evaluate(d)
+        be.set_subchunk(300)
+        e_300 = be.evaluate(d)
+        torch.cuda.synchronize()
+        assert int(st.abs().sum()) == 0
+        assert torch.equal(e_auto, e_off) and torch.equal(e_auto, e_300)
+        os.environ["PIRL_NO_REGTILE"] = "1"
+        try:
+            ref = pkg.RCWABatch(256, order, max_batch=256, device=0)
+        finally:
+            del os.environ["PIRL_NO_REGTILE"]
+        e_ref, r3_ref, t3_ref, _ = ref.evaluate(d[:256], return_orders=True)
+        torch.cuda.synchronize()
+        assert float((e_ref - e_auto[:256]).abs().max()) <= TIGHT
+        assert float((r3_ref - r3[:256]).abs().max()) <= TIGHT and float((t3_ref - t3[:256]).abs().max()) <= TIGHT
+        # lossless structure: the three reported orders never exceed unity and the efficiencies are non-negative
+        assert float(e_auto.min()) >= 0.0 and float((r3.sum(1) + t3.sum(1)).max()) <= 1.0 + 1e-9
+        be.close(); ref.close()
