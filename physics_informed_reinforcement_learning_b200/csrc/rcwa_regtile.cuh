@@ -53,6 +53,11 @@ struct FrontSmem {
   static __host__ __device__ constexpr int doubles(int n_cells) { return tw + 2 * n_cells + pirl_even((n_cells + 7) / 8); }
 };
 
+#ifdef PIRL_HH_PHASES
+#define HH_PHASE(n) RK_PHASE(n)
+#else
+#define HH_PHASE(n) do { } while (0)
+#endif
 #define RK_PHASE(n)                                                                       \
   do {                                                                                    \
     if (P.phase_clk && tid == 0) {                                                        \
@@ -339,7 +344,9 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
             if (a >= ka) { const int i = ti + TR * a; if (i > k) xb[i] = t[a][kb]; }
           if (ti == kti) dd[k] = t[ka][kb];
         }
+        HH_PHASE(16);
         __syncthreads();
+        HH_PHASE(17);
         double s = 0.0;
         for (int i = k + 1 + lane; i < FF; i += 32) { const double x = xb[i]; s = fma(x, x, s); }
         s = warp_sum(s);
@@ -352,6 +359,7 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
         const double alpha = -copysign(sqrt(s), x0);
         const double v0 = x0 - alpha;
         const double beta = 1.0 / (s - alpha * x0);
+        HH_PHASE(18);
         double vi[RT], vj[CT];
 #pragma unroll
         for (int a = 0; a < RT; ++a)
@@ -369,24 +377,39 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
               if (b >= kb) acc = fma(t[a][b], vj[b], acc);
             if (act) red[(ti + TR * a) * TC + tj] = acc;
           }
+        HH_PHASE(19);
         __syncthreads();
-        if (tid < FF) {
+        HH_PHASE(20);
+        // rows: p = beta C22 v; the same (FF + 31) / 32 warps also reduce v . p (for kk), so that no second all-warp reduction
+        // sits between the barrier and the rank-2 update
+        constexpr int NWR = (FF + 31) / 32;
+        if (tid < 32 * NWR) {
           const int r = tid;
-          if (r > k) {
+          double contrib = 0.0;
+          if (r < FF && r > k) {
             double acc = 0.0;
 #pragma unroll
             for (int c = 0; c < TC; ++c) acc += red[r * TC + c];
-            pvec[r] = beta * acc;
-            Lsm[k * LD + r] = (r == k + 1) ? v0 : xb[r];     // reflector -> upper triangle of the shared matrix
+            const double vr = (r == k + 1) ? v0 : xb[r];
+            const double pr_ = beta * acc;
+            pvec[r] = pr_;
+            contrib = pr_ * vr;
+            Lsm[k * LD + r] = vr;                             // reflector -> upper triangle of the shared matrix
           } else if (r == k) {
             Lsm[k * LD + k] = beta;
             ee[k] = alpha;
           }
+          contrib = warp_sum(contrib);
+          if (lane == 0) scal[tid >> 5] = contrib;
         }
+        HH_PHASE(21);
         __syncthreads();
+        HH_PHASE(22);
         double kk = 0.0;
-        for (int i = k + 1 + lane; i < FF; i += 32) kk = fma(pvec[i], (i == k + 1) ? v0 : xb[i], kk);
-        kk = 0.5 * beta * warp_sum(kk);
+#pragma unroll
+        for (int w = 0; w < NWR; ++w) kk += scal[w];
+        kk *= 0.5 * beta;
+        HH_PHASE(23);
         double wi[RT];
 #pragma unroll
         for (int a = 0; a < RT; ++a)
@@ -400,6 +423,7 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
             for (int a = 0; a < RT; ++a)
               if (a >= ka) t[a][b] = fma(-vi[a], wjb, fma(-wi[a], vj[b], t[a][b]));
           }
+        HH_PHASE(24);
       }
     }
     // trailing 2x2 block
