@@ -338,17 +338,60 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
         if (k > FF - 3) break;
         const int kti = k - ka * TR;
         double* xb = colbuf + (k & 1) * FE;
+        double* c2 = rowbuf + (k & 1) * FE;      // column k+1 of the trailing matrix (rows > k)
         if (act && tj == kj) {
 #pragma unroll
           for (int a = 0; a < RT; ++a)
             if (a >= ka) { const int i = ti + TR * a; if (i > k) xb[i] = t[a][kb]; }
           if (ti == kti) dd[k] = t[ka][kb];
         }
+        if (act) {                               // column k+1 sits in this column block, or is the first of the next one
+          const int kbn = (kb + 1 < CT) ? kb + 1 : kb;   // constant after unrolling
+          if (kj + 1 < TC) {
+            if (tj == kj + 1) {
+#pragma unroll
+              for (int a = 0; a < RT; ++a)
+                if (a >= ka) { const int i = ti + TR * a; if (i > k) c2[i] = t[a][kb]; }
+            }
+          } else if (tj == 0) {
+#pragma unroll
+            for (int a = 0; a < RT; ++a)
+              if (a >= ka) { const int i = ti + TR * a; if (i > k) c2[i] = t[a][kbn]; }
+          }
+        }
         HH_PHASE(16);
         __syncthreads();
         HH_PHASE(17);
+        // Two independent chains after the barrier, written as straight-line code so that they interleave:
+        //  (A) s = |x|^2 -> alpha, v0, beta (loads, five shuffle levels, sqrt, division)
+        //  (B) partial row sums of C22 x with the UN-normalised column x: v = x - alpha e_{k+1} gives
+        //      C22 v = C22 x - alpha C22[:, k+1], and the correction is applied by the row-sum threads after the next barrier.
         double s = 0.0;
-        for (int i = k + 1 + lane; i < FF; i += 32) { const double x = xb[i]; s = fma(x, x, s); }
+        {
+          constexpr int NS = (FF + 31) / 32;
+#pragma unroll
+          for (int u = 0; u < NS; ++u) {
+            const int i = k + 1 + lane + 32 * u;
+            const double x = (i < FF) ? xb[i] : 0.0;
+            s = fma(x, x, s);
+          }
+        }
+        double vi[RT], vj[CT];
+#pragma unroll
+        for (int a = 0; a < RT; ++a)
+          if (a >= ka) { const int i = ti + TR * a; vi[a] = (i > k) ? xb[i] : 0.0; }
+#pragma unroll
+        for (int b = 0; b < CT; ++b)
+          if (b >= kb) { const int j = tj + TC * b; vj[b] = (j > k) ? xb[j] : 0.0; }
+#pragma unroll
+        for (int a = 0; a < RT; ++a)
+          if (a >= ka) {
+            double acc = 0.0;
+#pragma unroll
+            for (int b = 0; b < CT; ++b)
+              if (b >= kb) acc = fma(t[a][b], vj[b], acc);
+            if (act) red[(ti + TR * a) * TC + tj] = acc;
+          }
         s = warp_sum(s);
         const double x0 = xb[k + 1];
         const double tail2 = s - x0 * x0;
@@ -360,23 +403,13 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
         const double v0 = x0 - alpha;
         const double beta = 1.0 / (s - alpha * x0);
         HH_PHASE(18);
-        double vi[RT], vj[CT];
+        // v differs from x only in entry k+1
 #pragma unroll
         for (int a = 0; a < RT; ++a)
-          if (a >= ka) { const int i = ti + TR * a; vi[a] = (i > k) ? ((i == k + 1) ? v0 : xb[i]) : 0.0; }
+          if (a >= ka) { if (ti + TR * a == k + 1) vi[a] = v0; }
 #pragma unroll
         for (int b = 0; b < CT; ++b)
-          if (b >= kb) { const int j = tj + TC * b; vj[b] = (j > k) ? ((j == k + 1) ? v0 : xb[j]) : 0.0; }
-        // partial row sums of C22 v
-#pragma unroll
-        for (int a = 0; a < RT; ++a)
-          if (a >= ka) {
-            double acc = 0.0;
-#pragma unroll
-            for (int b = 0; b < CT; ++b)
-              if (b >= kb) acc = fma(t[a][b], vj[b], acc);
-            if (act) red[(ti + TR * a) * TC + tj] = acc;
-          }
+          if (b >= kb) { if (tj + TC * b == k + 1) vj[b] = v0; }
         HH_PHASE(19);
         __syncthreads();
         HH_PHASE(20);
@@ -390,6 +423,7 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
             double acc = 0.0;
 #pragma unroll
             for (int c = 0; c < TC; ++c) acc += red[r * TC + c];
+            acc = fma(-alpha, c2[r], acc);                    // C22 v = C22 x - alpha C22[:, k+1]
             const double vr = (r == k + 1) ? v0 : xb[r];
             const double pr_ = beta * acc;
             pvec[r] = pr_;
