@@ -39,6 +39,7 @@ class SimpleQConfig:
     timesteps_per_update: int = 32             # :71-73: 16 rollout workers x rollout_fragment_length 2 sampled per train batch
     max_updates_per_iter: int = 64             # cap on learner updates after one vector-env step (B * world timesteps)
     seed: int = 42                             # utils.py:14-18 seed_all
+    cuda_graph: bool = True                    # replay forward + backward of the learner step from a CUDA graph (CUDA only)
 
 
 def epsilon_at(cfg: SimpleQConfig, timestep: int) -> float:
@@ -90,7 +91,14 @@ class SimpleQTrainer:
         self.target = copy.deepcopy(self.model).eval()
         for p in self.target.parameters():
             p.requires_grad_(False)
-        self.opt = torch.optim.Adam(self.model.parameters(), lr=self.cfg.lr)
+        on_cuda = self.device.type == "cuda"
+        self.opt = torch.optim.Adam(self.model.parameters(), lr=self.cfg.lr, fused=True) if on_cuda else \
+            torch.optim.Adam(self.model.parameters(), lr=self.cfg.lr)
+        # learner step as a CUDA graph (the Q-network is ~600 small launches per update: launch bound at batch 512 / world)
+        self.use_graph = on_cuda and self.cfg.cuda_graph
+        self._graph = None
+        self._static = None
+        self._graph_warmup = 0
         self.replay = DeviceReplay(max(self.cfg.replay_capacity // self.world, env.B), env.n_cells, self.device)
         self.gen = torch.Generator(device=self.device)
         self.gen.manual_seed(self.cfg.seed + 1000 * self.rank)
@@ -113,31 +121,67 @@ class SimpleQTrainer:
         explore = torch.rand(greedy.shape, device=q.device, generator=self.gen) < epsilon
         return torch.where(explore, rnd, greedy)
 
+    def _loss(self, obs, act, rew, nxt, done):
+        cfg = self.cfg
+        q = self.model(obs).gather(1, act[:, None]).squeeze(1)
+        with torch.no_grad():
+            qn = self.target(nxt).max(dim=1).values
+            tgt = rew + cfg.gamma * (1.0 - done) * qn
+        return nn.functional.huber_loss(q, tgt)
+
+    def _allreduce_grads(self):
+        if self.world == 1:
+            return
+        grads = [p.grad for p in self.model.parameters() if p.grad is not None]
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat)
+        flat /= self.world
+        torch._foreach_copy_(grads, [f.view_as(g) for f, g in zip(flat.split([g.numel() for g in grads]), grads)])
+
     def learn(self):
         cfg = self.cfg
         b = max(cfg.train_batch_size // self.world, 1)
         obs, act, rew, nxt, done = self.replay.sample(b, self.gen)
+        obs, nxt, done = obs.to(torch.float32), nxt.to(torch.float32), done.to(torch.float32)
         self.model.train()
-        q = self.model(obs.to(torch.float32)).gather(1, act[:, None]).squeeze(1)
-        with torch.no_grad():
-            qn = self.target(nxt.to(torch.float32)).max(dim=1).values
-            tgt = rew + cfg.gamma * (~done).to(torch.float32) * qn
-        loss = nn.functional.huber_loss(q, tgt)
-        self.opt.zero_grad(set_to_none=True)
-        loss.backward()
-        if self.world > 1:
-            flat = torch.cat([p.grad.reshape(-1) for p in self.model.parameters() if p.grad is not None])
-            dist.all_reduce(flat)
-            flat /= self.world
-            o = 0
-            for p in self.model.parameters():
-                if p.grad is not None:
-                    n = p.grad.numel()
-                    p.grad.copy_(flat[o:o + n].view_as(p.grad))
-                    o += n
+        if not self.use_graph:
+            loss = self._loss(obs, act, rew, nxt, done)
+            self.opt.zero_grad(set_to_none=True)
+            loss.backward()
+            self._allreduce_grads()
+            self.opt.step()
+            self.updates += 1
+            return loss.detach()
+        # ---- CUDA-graph path: static input tensors, forward + backward captured once (after three eager warm-up updates on a
+        #      side stream, as torch.cuda.graphs requires); gradient all_reduce and the fused Adam step stay outside the graph ----
+        if self._static is None:
+            self._static = [torch.empty_like(t) for t in (obs, act, rew, nxt, done)]
+        for st_, src in zip(self._static, (obs, act, rew, nxt, done)):
+            st_.copy_(src)
+        if self._graph is None:
+            if self._graph_warmup < 3:
+                side = torch.cuda.Stream(self.device)
+                side.wait_stream(torch.cuda.current_stream(self.device))
+                with torch.cuda.stream(side):
+                    self.opt.zero_grad(set_to_none=True)
+                    loss = self._loss(*self._static)
+                    loss.backward()
+                torch.cuda.current_stream(self.device).wait_stream(side)
+                self._graph_warmup += 1
+                self._allreduce_grads()
+                self.opt.step()
+                self.updates += 1
+                return loss.detach()
+            self.opt.zero_grad(set_to_none=True)
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self._static_loss = self._loss(*self._static)
+                self._static_loss.backward()
+        self._graph.replay()
+        self._allreduce_grads()
         self.opt.step()
         self.updates += 1
-        return loss.detach()
+        return self._static_loss.detach().clone()
 
     @torch.no_grad()
     def sync_target(self):

@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--data_dir", type=str, default="runs/simple_q")
     ap.add_argument("--log_every", type=int, default=50)
     ap.add_argument("--seed", type=int, default=42)
+    ap.add_argument("--no_cuda_graph", action="store_true", help="run the learner step eagerly")
     ap.add_argument("--timesteps_per_update", type=int, default=32,
                     help="sampled env steps per learner update (reference: 16 workers x fragment length 2)")
     args = ap.parse_args()
@@ -53,7 +54,7 @@ def main():
     model = {"unet": lambda: ShallowUQNet(args.n_cells), "fcn": lambda: FCNQNet(args.n_cells),
              "fcn_heavy": lambda: FCNQNet(args.n_cells, 1200)}[args.model]()
     loaded = load_pretrained(model, args.pretrained_ckpt)
-    trainer = SimpleQTrainer(env, model, SimpleQConfig(seed=args.seed, timesteps_per_update=args.timesteps_per_update), log_dir=args.data_dir)
+    trainer = SimpleQTrainer(env, model, SimpleQConfig(seed=args.seed, timesteps_per_update=args.timesteps_per_update, cuda_graph=not args.no_cuda_graph), log_dir=args.data_dir)
     out = trainer.train(args.train_steps, log_every=args.log_every)
     path = trainer.save_best()
     if rank == 0:
