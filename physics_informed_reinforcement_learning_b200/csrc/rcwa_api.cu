@@ -363,6 +363,7 @@ static KParams sub_params(const KParams& P0, int n_cells, int ff, int off, int c
   P.rot_cs += (size_t)off * P.maxrot; P.sweeps += (size_t)off * P.maxsw;
   P.nrot += off; P.nsw += off; P.wstatus += off;
   P.eff += off;
+  if (P.Einv) P.Einv += off * m2;
   if (P.de_r3) P.de_r3 += 3 * (size_t)off;
   if (P.de_t3) P.de_t3 += 3 * (size_t)off;
   if (P.status) P.status += off;
@@ -456,9 +457,37 @@ static KParams chunk_params(pirl_handle* h, const int8_t* patterns, const double
   return P;
 }
 
-static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* params, int pstride, int Bc,
-                        double* eff, double* de_r3, double* de_t3, int32_t* status, cudaStream_t st) {
-  KParams P = chunk_params(h, patterns, params, pstride, Bc, eff, de_r3, de_t3, status);
+static constexpr int GTAIL_NT = 512, GEIG_NT = 256;
+
+// gradient workspaces of the sub-chunk [off, ...): same offsets as sub_params
+static GParams sub_gparams(const GParams& G0, int n_cells, int ff, int off) {
+  GParams G = G0;
+  G.lamb += (size_t)off * ff;
+  G.Lf += (size_t)off * ff * PIRL_GRAD_RANK; G.Rf += (size_t)off * ff * PIRL_GRAD_RANK; G.Vf += (size_t)off * ff * PIRL_GRAD_NV;
+  G.grad += (size_t)off * n_cells;
+  return G;
+}
+
+static void launch_gtail(pirl_handle* h, const KParams& P, GParams G, cudaStream_t st) {
+  StageTimer t(h, 7, st);
+  G.gscratch = h->g_scr_tail; G.gstride = h->g_tail_stride; G.smem_mats = h->g_tail_mats;
+  const int g = std::min(P.B, h->g_tail_grid);
+  if (h->ff <= 96) g_tail<GTAIL_NT, 3><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
+  else if (h->ff <= 128) g_tail<GTAIL_NT, 4><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
+  else g_tail<GTAIL_NT, 8><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
+  h->launches += 1;
+}
+
+static void launch_geig(pirl_handle* h, const KParams& P, GParams G, cudaStream_t st) {
+  StageTimer t(h, 8, st);
+  G.gscratch = h->g_scr_eig; G.gstride = h->g_eig_stride; G.smem_mats = h->g_eig_mats;
+  g_eigback<GEIG_NT><<<std::min(P.B, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
+  h->launches += 1;
+}
+
+// One chunk.  G0 == nullptr: forward path (tails = rk_tail2 / k_tail).  G0 != nullptr: adjoint-gradient path (tails = g_tail on
+// each sub-chunk, then g_eigback on the whole chunk); P0 then carries P.Einv.
+static int launch_chunk(pirl_handle* h, KParams P, int Bc, cudaStream_t st, const GParams* G0 = nullptr) {
 
   // Sub-chunk pipeline.  k_ql is one thread per structure and purely latency bound (about 3 ms whatever the batch), so a
   // chunk is cut into sub-chunks: all front kernels are issued first on the caller's stream, each sub-chunk's k_ql runs on
@@ -471,7 +500,8 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
   if (nsub <= 1) {
     launch_front(h, P, st);
     launch_ql(h, P, st);
-    launch_back(h, P, st);
+    if (!G0) launch_back(h, P, st);
+    else { launch_apply(h, P, st); launch_gtail(h, P, *G0, st); launch_geig(h, P, *G0, st); }
   } else {
     // Order on the device: fronts of all sub-chunks back to back (each on its own stream so that the persistent CTAs of
     // sub-chunk c+1 backfill the SMs as those of c drain), k_ql(c) on a high-priority side stream as soon as front(c) is done
@@ -499,10 +529,15 @@ static int launch_chunk(pirl_handle* h, const int8_t* patterns, const double* pa
       CUDA_TRY(cudaStreamWaitEvent(st, h->evQ[c], 0));
       launch_apply(h, Ps[c], st);
     }
-    launch_tail(h, sub_params(P, h->cfg.n_cells, h->ff, 0, (nsub - 1) * per), st);
+    if (!G0) launch_tail(h, sub_params(P, h->cfg.n_cells, h->ff, 0, (nsub - 1) * per), st);
+    else launch_gtail(h, sub_params(P, h->cfg.n_cells, h->ff, 0, (nsub - 1) * per), *G0, st);
     CUDA_TRY(cudaStreamWaitEvent(st, h->evQ[nsub - 1], 0));
     launch_apply(h, Ps[nsub - 1], st);
-    launch_tail(h, Ps[nsub - 1], st);
+    if (!G0) launch_tail(h, Ps[nsub - 1], st);
+    else {
+      launch_gtail(h, Ps[nsub - 1], sub_gparams(*G0, h->cfg.n_cells, h->ff, (nsub - 1) * per), st);
+      launch_geig(h, P, *G0, st);
+    }
   }
   h->last_chunk = Bc;
   CUDA_TRY(cudaGetLastError());
@@ -548,9 +583,9 @@ extern "C" int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const doub
   const int64_t mb = h->cfg.max_batch;
   for (int64_t off = 0; off < B; off += mb) {
     const int Bc = (int)std::min<int64_t>(mb, B - off);
-    int rc = launch_chunk(h, patterns + off * h->cfg.n_cells, params + off * param_stride, param_stride, Bc,
-                          eff + off, de_r3 ? de_r3 + 3 * off : nullptr, de_t3 ? de_t3 + 3 * off : nullptr,
-                          status ? status + off : nullptr, st);
+    int rc = launch_chunk(h, chunk_params(h, patterns + off * h->cfg.n_cells, params + off * param_stride, param_stride, Bc,
+                                          eff + off, de_r3 ? de_r3 + 3 * off : nullptr, de_t3 ? de_t3 + 3 * off : nullptr,
+                                          status ? status + off : nullptr), Bc, st);
     if (rc) return rc;
   }
   return 0;
@@ -666,7 +701,6 @@ extern "C" int pirl_rcwa_debug_fetch(pirl_handle* h, int32_t what, double* dst, 
 // ---------------------------------------------------------------------------------------------------
 // adjoint gradient
 // ---------------------------------------------------------------------------------------------------
-static constexpr int GTAIL_NT = 512, GEIG_NT = 256;
 
 template <typename K>
 static int plan_grad_kernel(pirl_handle* h, K kern, int nt, size_t vec_bytes, size_t mat_bytes, int want, int* mats,
@@ -727,25 +761,7 @@ extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const
     P.Einv = h->g_Einv;
     GParams G;
     G.lamb = h->g_lamb; G.Lf = h->g_Lf; G.Rf = h->g_Rf; G.Vf = h->g_Vf; G.grad = grad + off * h->cfg.n_cells;
-    launch_front(h, P, st);
-    launch_ql(h, P, st);
-    launch_apply(h, P, st);
-    {
-      StageTimer t(h, 7, st);
-      G.gscratch = h->g_scr_tail; G.gstride = h->g_tail_stride; G.smem_mats = h->g_tail_mats;
-      const int g = std::min(Bc, h->g_tail_grid);
-      if (ff <= 96) g_tail<GTAIL_NT, 3><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
-      else if (ff <= 128) g_tail<GTAIL_NT, 4><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
-      else g_tail<GTAIL_NT, 8><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
-    }
-    {
-      StageTimer t(h, 8, st);
-      G.gscratch = h->g_scr_eig; G.gstride = h->g_eig_stride; G.smem_mats = h->g_eig_mats;
-      g_eigback<GEIG_NT><<<std::min(Bc, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
-    }
-    h->launches += 2;
-    h->last_chunk = Bc;
-    CUDA_TRY(cudaGetLastError());
+    if (int rc = launch_chunk(h, P, Bc, st, &G)) return rc;
   }
   return 0;
 }
