@@ -41,6 +41,21 @@ __host__ __device__ inline size_t grad_eig_scratch_doubles(int ff, int ld) { ret
 
 __device__ __forceinline__ cplx cconj(cplx a) { return make_double2(a.x, -a.y); }
 
+// 1 / z for the pivots of the elimination loops: hardware seed + two Newton steps (full double accuracy up to an ulp or
+// two, no slow path; the IEEE division is ~4x longer and sits on the critical path of every elimination step)
+__device__ __forceinline__ double rcp_newton(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  return fma(r, e, r);
+}
+__device__ __forceinline__ cplx cinv_fast(cplx a) {
+  const double d = rcp_newton(fma(a.x, a.x, a.y * a.y));
+  return make_double2(a.x * d, -a.y * d);
+}
+
 // y_i = sum_j M[i][j] x_j (+ diag_i x_i): one warp per row.  M complex symmetric in every use, so this also serves M^T x.
 template <int NT>
 __device__ __forceinline__ void cta_symv(const cplx* M, int ld, const cplx* x, cplx* y, int ff, const cplx* diag = nullptr) {
@@ -75,112 +90,210 @@ __device__ __forceinline__ void ctile_store(const cplx (&t)[RA][CC], cplx* M, in
   }
 }
 
-// in-place inverse by Gauss-Jordan without pivoting (complex symmetric G with a dominant diagonal)
+// All tile indices below are compile-time constants after unrolling (the step index is split as k = 16 KB + kk with KB
+// unrolled): a run-time row / column slot makes the compiler index the tile in local memory and re-store it every step.
+//
+// publish row k (owner warp) and column k (owner lanes) of the tile; KA = k >> 4 is a constant at every call site
 template <int RA, int CC>
-__device__ __forceinline__ void ctile_gj_inverse(cplx (&t)[RA][CC], cplx* rowk, cplx* colk, int ff, int w, int lane) {
-  for (int k = 0; k < ff; ++k) {
-    const int ka = k >> 4, kw = k & 15, kc = k >> 5, kl = k & 31;
-    __syncthreads();
-    if (w == kw) {
+__device__ __forceinline__ void ctile_publish(const cplx (&t)[RA][CC], cplx* rowk, cplx* colk, int k, const int KA, int ff, int w, int lane) {
+  const int KC = KA >> 1;
+  if (w == (k & 15)) {
 #pragma unroll
-      for (int a = 0; a < RA; ++a)
-        if (a == ka) {
+    for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; if (j < ff) rowk[j] = t[KA][c]; }
+  }
+  if (lane == (k & 31)) {
 #pragma unroll
-          for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; if (j < ff) rowk[j] = t[a][c]; }
-        }
-    }
-    if (lane == kl) {
+    for (int a = 0; a < RA; ++a) { const int i = w + 16 * a; if (i < ff) colk[i] = t[a][KC]; }
+  }
+}
+
+// in-place inverse by Gauss-Jordan without pivoting (complex symmetric G with a dominant diagonal).  One barrier per step:
+// the owners publish row / column k + 1 right after their update of step k into the other pair of buffers, and the owner of
+// the next pivot computes its reciprocal one step ahead (pslot), off the critical path.
+template <int RA, int CC>
+__device__ __forceinline__ void ctile_gj_inverse(cplx (&t)[RA][CC], cplx* rc0, cplx* rc1, cplx* rc2, cplx* rc3, cplx* pslot, int ff, int w,
+                                                 int lane) {
+  __syncthreads();
+  ctile_publish<RA, CC>(t, rc0, rc1, 0, 0, ff, w, lane);
+  if (w == 0 && lane == 0) pslot[0] = cinv_fast(t[0][0]);
+  __syncthreads();
+  const int nra = (ff - w + 15) >> 4;              // row slots of this warp that hold a row (warp-uniform)
 #pragma unroll
-      for (int c = 0; c < CC; ++c)
-        if (c == kc) {
+  for (int KB = 0; KB < RA; ++KB) {
+#pragma unroll 1
+    for (int kk = 0; kk < 16; ++kk) {
+      const int k = 16 * KB + kk;
+      if (k >= ff) break;
+      const cplx* rowk = (k & 1) ? rc2 : rc0;
+      const cplx* colk = (k & 1) ? rc3 : rc1;
+      const cplx piv = rowk[k];
+      const cplx p = pslot[k & 1];
+      const int k1 = k + 1;
+      if (k1 < ff && w == (k1 & 15) && lane == (k1 & 31)) {
+        cplx told;
+        if (kk < 15) told = t[KB][KB >> 1];
+        else told = t[(KB + 1 < RA) ? KB + 1 : KB][(KB + 1 < RA) ? ((KB + 1) >> 1) : 0];
+        const cplx cvn = cscale(cmul(colk[k1], p), -1.0);
+        pslot[k1 & 1] = cinv_fast(cfma(cvn, rowk[k1], told));
+      }
+      cplx rv[CC];
 #pragma unroll
-          for (int a = 0; a < RA; ++a) { const int i = w + 16 * a; if (i < ff) colk[i] = t[a][c]; }
-        }
-    }
-    __syncthreads();
-    const cplx piv = rowk[k];
-    const cplx p = cinv(piv);
-    cplx rv[CC];
+      for (int c = 0; c < CC; ++c) {
+        const int j = lane + 32 * c;
+        rv[c] = (j < ff) ? ((j == k) ? make_double2(1.0 + piv.x, piv.y) : rowk[j]) : make_double2(0.0, 0.0);
+      }
 #pragma unroll
-    for (int c = 0; c < CC; ++c) {
-      const int j = lane + 32 * c;
-      rv[c] = (j < ff) ? ((j == k) ? make_double2(1.0 + piv.x, piv.y) : rowk[j]) : make_double2(0.0, 0.0);
-    }
+      for (int a = 0; a < RA; ++a) {
+        if (a >= nra) continue;
+        const int i = w + 16 * a;
+        const cplx cv = (i == k) ? make_double2(p.x - 1.0, p.y) : cscale(cmul(colk[i], p), -1.0);
 #pragma unroll
-    for (int a = 0; a < RA; ++a) {
-      const int i = w + 16 * a;
-      cplx cv = make_double2(0.0, 0.0);
-      if (i < ff) cv = (i == k) ? make_double2(p.x - 1.0, p.y) : cscale(cmul(colk[i], p), -1.0);
-#pragma unroll
-      for (int c = 0; c < CC; ++c) t[a][c] = cfma(cv, rv[c], t[a][c]);
+        for (int c = 0; c < CC; ++c) t[a][c] = cfma(cv, rv[c], t[a][c]);
+      }
+      if (k1 < ff) {
+        if (kk < 15) ctile_publish<RA, CC>(t, (k & 1) ? rc0 : rc2, (k & 1) ? rc1 : rc3, k1, KB, ff, w, lane);
+        else ctile_publish<RA, CC>(t, (k & 1) ? rc0 : rc2, (k & 1) ? rc1 : rc3, k1, (KB + 1 < RA) ? KB + 1 : KB, ff, w, lane);
+      }
+      __syncthreads();
     }
   }
-  __syncthreads();
 }
 
 // LU with implicit partial pivoting: rows are never moved; rperm[k] = pivot row of step k.  Multipliers are left in column k
 // of the rows still unused, the pivot rows hold U.  The right-hand side bvec (shared) is eliminated alongside.
+// Two barriers per step: column k + 1 and its magnitudes are published right after the update of step k (buffers alternate).
 template <int RA, int CC>
-__device__ __forceinline__ void ctile_lu_implicit(cplx (&t)[RA][CC], cplx* rowk, cplx* colk, double* magk, cplx* bvec, int* rperm,
-                                                  int ff, int w, int lane) {
+__device__ __forceinline__ void ctile_lu_publish_col(const cplx (&t)[RA][CC], cplx* colk, double* magk, unsigned used, int k, const int KC,
+                                                     int ff, int w, int lane) {
+  if (lane == (k & 31)) {
+#pragma unroll
+    for (int a = 0; a < RA; ++a) {
+      const int i = w + 16 * a;
+      if (i < ff) { colk[i] = t[a][KC]; magk[i] = ((used >> a) & 1u) ? -1.0 : fabs(t[a][KC].x) + fabs(t[a][KC].y); }
+    }
+  }
+}
+
+template <int RA, int CC>
+__device__ __forceinline__ void ctile_lu_implicit(cplx (&t)[RA][CC], cplx* rowk, cplx* colk0, cplx* colk1, double* magk0, double* magk1,
+                                                  cplx* bvec, int* rperm, int ff, int w, int lane) {
   unsigned used = 0;
 #pragma unroll
   for (int a = 0; a < RA; ++a) if (w + 16 * a >= ff) used |= 1u << a;
-  for (int k = 0; k < ff; ++k) {
-    const int kc = k >> 5, kl = k & 31;
-    __syncthreads();
-    if (lane == kl) {
+  __syncthreads();
+  ctile_lu_publish_col<RA, CC>(t, colk0, magk0, used, 0, 0, ff, w, lane);
+  __syncthreads();
 #pragma unroll
-      for (int c = 0; c < CC; ++c)
-        if (c == kc) {
+  for (int KC = 0; KC < CC; ++KC) {
+#pragma unroll 1
+    for (int kk = 0; kk < 32; ++kk) {
+      const int k = 32 * KC + kk;
+      if (k >= ff) break;
+      const cplx* colk = (k & 1) ? colk1 : colk0;
+      const double* magk = (k & 1) ? magk1 : magk0;
+      // every warp finds the same pivot (largest |re| + |im| among the unused rows, lowest row on ties)
+      double best = -2.0; int pv = 0;
+      for (int i = lane; i < ff; i += 32) { const double m = magk[i]; if (m > best) { best = m; pv = i; } }
 #pragma unroll
-          for (int a = 0; a < RA; ++a) {
-            const int i = w + 16 * a;
-            if (i < ff) { colk[i] = t[a][c]; magk[i] = ((used >> a) & 1u) ? -1.0 : fabs(t[a][c].x) + fabs(t[a][c].y); }
-          }
-        }
-    }
-    __syncthreads();
-    // every warp finds the same pivot (largest |re| + |im| among the unused rows, lowest row on ties)
-    double best = -2.0; int pv = 0;
-    for (int i = lane; i < ff; i += 32) { const double m = magk[i]; if (m > best) { best = m; pv = i; } }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, pv, o);
-      if (ob > best || (ob == best && oi < pv)) { best = ob; pv = oi; }
-    }
-    const int pa = pv >> 4, pw = pv & 15;
-    if (w == pw) {
-#pragma unroll
-      for (int a = 0; a < RA; ++a)
-        if (a == pa) {
-#pragma unroll
-          for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; if (j < ff) rowk[j] = t[a][c]; }
-        }
-      used |= 1u << pa;
-      if (lane == 0) rperm[k] = pv;
-    }
-    __syncthreads();
-    const cplx pinv = cinv(rowk[k]);
-    const cplx bk = bvec[pv];
-    cplx rv[CC];
-#pragma unroll
-    for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; rv[c] = (j < ff && j > k) ? rowk[j] : make_double2(0.0, 0.0); }
-#pragma unroll
-    for (int a = 0; a < RA; ++a) {
-      if ((used >> a) & 1u) continue;          // warp-uniform
-      const int i = w + 16 * a;
-      const cplx f = cmul(colk[i], pinv);
-#pragma unroll
-      for (int c = 0; c < CC; ++c) {
-        t[a][c] = cfnma(f, rv[c], t[a][c]);
-        if (lane + 32 * c == k) t[a][c] = f;
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, pv, o);
+        if (ob > best || (ob == best && oi < pv)) { best = ob; pv = oi; }
       }
-      if (lane == 0) bvec[i] = cfnma(f, bk, bvec[i]);
+      const int pa = pv >> 4;
+      if (w == (pv & 15)) {
+        // the pivot row sits in a run-time slot: chain of value selects over the slots (no run-time tile index)
+        cplx rowv[CC];
+#pragma unroll
+        for (int c = 0; c < CC; ++c) rowv[c] = t[0][c];
+#pragma unroll
+        for (int a = 1; a < RA; ++a)
+#pragma unroll
+          for (int c = 0; c < CC; ++c) { rowv[c].x = (pa == a) ? t[a][c].x : rowv[c].x; rowv[c].y = (pa == a) ? t[a][c].y : rowv[c].y; }
+#pragma unroll
+        for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; if (j < ff) rowk[j] = rowv[c]; }
+        used |= 1u << pa;
+        if (lane == 0) rperm[k] = pv;
+      }
+      __syncthreads();
+      const cplx pinv = cinv_fast(rowk[k]);
+      const cplx bk = bvec[pv];
+      cplx rv[CC];
+#pragma unroll
+      for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; rv[c] = (j < ff && j > k) ? rowk[j] : make_double2(0.0, 0.0); }
+#pragma unroll
+      for (int a = 0; a < RA; ++a) {
+        if ((used >> a) & 1u) continue;          // warp-uniform
+        const int i = w + 16 * a;
+        const cplx f = cmul(colk[i], pinv);
+#pragma unroll
+        for (int c = 0; c < CC; ++c) t[a][c] = cfnma(f, rv[c], t[a][c]);
+        if (lane == kk) t[a][KC] = f;
+        if (lane == 0) bvec[i] = cfnma(f, bk, bvec[i]);
+      }
+      if (k + 1 < ff) {
+        if (kk < 31) ctile_lu_publish_col<RA, CC>(t, (k & 1) ? colk0 : colk1, (k & 1) ? magk0 : magk1, used, k + 1, KC, ff, w, lane);
+        else ctile_lu_publish_col<RA, CC>(t, (k & 1) ? colk0 : colk1, (k & 1) ? magk0 : magk1, used, k + 1, (KC + 1 < CC) ? KC + 1 : KC, ff, w, lane);
+      }
+      __syncthreads();
     }
   }
-  __syncthreads();
+}
+
+// The two elimination loops run as real (not inlined) calls: inside the call only the tile and a handful of pointers are
+// live, so the 128-register budget of a 512-thread CTA holds the tile without spilling it every step (inlined into g_tail
+// the two dozen long-lived pointers of the kernel pushed the tile into local memory: 18 stores + 14 loads per step).
+template <int RA, int CC>
+struct CTile { cplx v[RA][CC]; };
+
+template <int RA, int CC>
+__device__ __noinline__ CTile<RA, CC> ctile_gj_call(CTile<RA, CC> T, cplx* rc0, cplx* rc1, cplx* rc2, cplx* rc3, cplx* pslot, int ff,
+                                                    int w, int lane) {
+  cplx t[RA][CC];   // explicit register copy: the by-value parameter itself stays in param (local) memory
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) t[a][c] = T.v[a][c];
+  ctile_gj_inverse<RA, CC>(t, rc0, rc1, rc2, rc3, pslot, ff, w, lane);
+  CTile<RA, CC> R;
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) R.v[a][c] = t[a][c];
+  return R;
+}
+template <int RA, int CC>
+__device__ __noinline__ CTile<RA, CC> ctile_lu_call(CTile<RA, CC> T, cplx* rowk, cplx* colk0, cplx* colk1, double* magk0, double* magk1,
+                                                    cplx* bvec, int* rperm, int ff, int w, int lane) {
+  cplx t[RA][CC];
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) t[a][c] = T.v[a][c];
+  ctile_lu_implicit<RA, CC>(t, rowk, colk0, colk1, magk0, magk1, bvec, rperm, ff, w, lane);
+  CTile<RA, CC> R;
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) R.v[a][c] = t[a][c];
+  return R;
+}
+
+template <int RA, int CC>
+__device__ __forceinline__ CTile<RA, CC> ctile_pack(const cplx (&t)[RA][CC]) {
+  CTile<RA, CC> T;
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) T.v[a][c] = t[a][c];
+  return T;
+}
+template <int RA, int CC>
+__device__ __forceinline__ void ctile_unpack(cplx (&t)[RA][CC], const CTile<RA, CC>& T) {
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) t[a][c] = T.v[a][c];
 }
 
 // ===================================================================================================
@@ -255,73 +368,155 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     }
     __syncthreads();
     const cplx r0 = make_double2(DI[z].x, DI[z].y + 1.0 / nI);
+    RK_PHASE(8);    // (slots 8-13 belong to rk_tail2 in the forward path, which does not run in a gradient call)
     if constexpr (REG) {
       cplx tl[RA][NCOL];
       // ---- G_II -> register tile, Hq and H_II -> global ----
+      // D is real on evanescent harmonics and imaginary on the few propagating ones: W^T Re(D) W is one real product with
+      // the harmonic index outermost (nine loads feed 36 multiply-adds); the imaginary rank-one parts are added at the end
+      int* lstI = ipiv;                                  // both lists are dead before the LU needs ipiv / magk
+      int* lstII = reinterpret_cast<int*>(magk);
+      if (warp == 0) {
+        int c1 = 0, c2 = 0;
+        for (int m0 = 0; m0 < ff; m0 += 32) {
+          const int m = m0 + lane;
+          const bool p1 = m < ff && DI[min(m, ff - 1)].y != 0.0, p2 = m < ff && DII[min(m, ff - 1)].y != 0.0;
+          const unsigned b1 = __ballot_sync(0xffffffffu, p1), b2 = __ballot_sync(0xffffffffu, p2);
+          const unsigned below = (1u << lane) - 1u;
+          if (p1) lstI[1 + c1 + __popc(b1 & below)] = m;
+          if (p2) lstII[1 + c2 + __popc(b2 & below)] = m;
+          c1 += __popc(b1); c2 += __popc(b2);
+        }
+        if (lane == 0) { lstI[0] = c1; lstII[0] = c2; }
+      }
+      {
+        double aI[RA][NCOL], aII[RA][NCOL];
 #pragma unroll
-      for (int a = 0; a < RA; ++a) {
-        const int i = warp + 16 * a;
-        cplx aI[NCOL], aII[NCOL];
+        for (int a = 0; a < RA; ++a)
 #pragma unroll
-        for (int c = 0; c < NCOL; ++c) { aI[c] = make_double2(0.0, 0.0); aII[c] = make_double2(0.0, 0.0); }
-        if (i < ff) {
-          for (int m = 0; m < ff; ++m) {
-            const double wi = Wr[m * ld + i];
-            const cplx d1 = DI[m], d2 = DII[m];
+          for (int c = 0; c < NCOL; ++c) { aI[a][c] = 0.0; aII[a][c] = 0.0; }
+        const int nra = (ff - warp + 15) >> 4;             // row slots of this warp that hold a row (warp-uniform)
+#pragma unroll 1
+        for (int m = 0; m < ff; ++m) {
+          const double d1 = DI[m].x, d2 = DII[m].x;
+          const double* wrow = Wr + m * ld;
+          double wj[NCOL];
+#pragma unroll
+          for (int c = 0; c < NCOL; ++c) wj[c] = wrow[min(lane + 32 * c, ff - 1)];
+#pragma unroll
+          for (int a = 0; a < RA; ++a) {
+            if (a >= nra) continue;
+            const double wi = wrow[warp + 16 * a];
+            const double w1 = wi * d1, w2 = wi * d2;
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) { aI[a][c] = fma(w1, wj[c], aI[a][c]); aII[a][c] = fma(w2, wj[c], aII[a][c]); }
+          }
+        }
+        RK_PHASE(9);
+        __syncthreads();                                   // lists visible
+        // imaginary parts: sum over the propagating harmonics of Im(D_m) w_m w_m^T, first medium I (-> Hq), then II
+#pragma unroll
+        for (int pass = 0; pass < 2; ++pass) {
+          const int* lst = pass ? lstII : lstI;
+          const cplx* Dm = pass ? DII : DI;
+          const int np = lst[0];
+          double im[RA][NCOL];
+#pragma unroll
+          for (int a = 0; a < RA; ++a)
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) im[a][c] = 0.0;
+          for (int e = 0; e < np; ++e) {
+            const int m = lst[1 + e];
+            const double beta = Dm[m].y;
+            const double* wrow = Wr + m * ld;
+            double wj[NCOL];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) wj[c] = wrow[min(lane + 32 * c, ff - 1)];
+#pragma unroll
+            for (int a = 0; a < RA; ++a) {
+              if (a >= nra) continue;
+              const double wi = wrow[warp + 16 * a] * beta;
+#pragma unroll
+              for (int c = 0; c < NCOL; ++c) im[a][c] = fma(wi, wj[c], im[a][c]);
+            }
+          }
+#pragma unroll
+          for (int a = 0; a < RA; ++a) {
+            const int i = warp + 16 * a;
 #pragma unroll
             for (int c = 0; c < NCOL; ++c) {
-              const int j = min(lane + 32 * c, ff - 1);
-              const double pr2 = wi * Wr[m * ld + j];
-              aI[c].x = fma(d1.x, pr2, aI[c].x); aI[c].y = fma(d1.y, pr2, aI[c].y);
-              aII[c].x = fma(d2.x, pr2, aII[c].x); aII[c].y = fma(d2.y, pr2, aII[c].y);
+              const int j = lane + 32 * c;
+              if (pass == 0) {
+                if (a < nra && j < ff) {
+                  cplx h = make_double2(aI[a][c], im[a][c]);
+                  if (i == j) h = csub(h, qv[i]);
+                  Hq[(size_t)i * ff + j] = h;
+                }
+              } else {
+                cplx g = make_double2(aII[a][c], im[a][c]);
+                if (a < nra && j < ff) {
+                  HII[(size_t)i * ff + j] = g;
+                  if (i == j) g = cadd(g, qv[i]);
+                }
+                tl[a][c] = g;
+              }
             }
           }
         }
-#pragma unroll
-        for (int c = 0; c < NCOL; ++c) {
-          const int j = lane + 32 * c;
-          cplx g = aII[c], h = aI[c];
-          if (i < ff && j < ff) {
-            HII[(size_t)i * ff + j] = g;
-            if (i == j) { g = cadd(g, qv[i]); h = csub(h, qv[i]); }
-            Hq[(size_t)i * ff + j] = h;
-          }
-          tl[a][c] = g;
-        }
       }
       RK_PHASE(16);
-      ctile_gj_inverse<RA, NCOL>(tl, rowk, colk, ff, warp, lane);
+      { const CTile<RA, NCOL> R_ = ctile_gj_call<RA, NCOL>(ctile_pack<RA, NCOL>(tl), rowk, colk, yv, dv, red, ff, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
       ctile_store<RA, NCOL>(tl, Pm, ld, ff, warp, lane);
+      // Hq X staged in S's storage (W is dead, the LU rows are written back much later)
+      for (int i = warp; i < ff; i += NW)
+        for (int k = lane; k < ff; k += 32) Sm[i * ld + k] = cmul(Hq[(size_t)i * ff + k], Xv[k]);
       __syncthreads();
       RK_PHASE(17);
       // ---- S = Hq (I - X^2) + 2Q + 2 (Hq X) P (X Q) -> register tile ----
+      // k outermost: per k three shared-memory loads of P and six broadcast loads of Hq X feed 18 complex multiply-adds
 #pragma unroll
-      for (int a = 0; a < RA; ++a) {
-        const int i = warp + 16 * a;
-        cplx acc[NCOL];
+      for (int a = 0; a < RA; ++a)
 #pragma unroll
-        for (int c = 0; c < NCOL; ++c) acc[c] = make_double2(0.0, 0.0);
-        const cplx* hrow = Hq + (size_t)min(i, ff - 1) * ff;
-        if (i < ff) {
-          for (int k = 0; k < ff; ++k) {
-            const cplx f = cmul(hrow[k], Xv[k]);
+        for (int c = 0; c < NCOL; ++c) tl[a][c] = make_double2(0.0, 0.0);
+      {
+        const int nra = (ff - warp + 15) >> 4;
+        const cplx* h0 = Hq + (size_t)warp * ff;           // row warp + 16 a starts at h0 + a * hstep
+        const int hstep = 16 * ff;
+        const cplx* a0 = Sm + warp * ld;
+        const int astep = 16 * ld;
+#pragma unroll 1
+        for (int k = 0; k < ff; ++k) {
+          cplx pk[NCOL];
 #pragma unroll
-            for (int c = 0; c < NCOL; ++c) acc[c] = cfma(f, Pm[k * ld + min(lane + 32 * c, ff - 1)], acc[c]);
+          for (int c = 0; c < NCOL; ++c) pk[c] = Pm[k * ld + min(lane + 32 * c, ff - 1)];
+#pragma unroll
+          for (int a = 0; a < RA; ++a) {
+            if (a >= nra) continue;                        // warp-uniform
+            const cplx f = a0[a * astep + k];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) tl[a][c] = cfma(f, pk[c], tl[a][c]);
           }
         }
+        RK_PHASE(10);
 #pragma unroll
-        for (int c = 0; c < NCOL; ++c) {
-          const int j = min(lane + 32 * c, ff - 1);
-          cplx sv = cmul(acc[c], XQ[j]);
-          sv = make_double2(2.0 * sv.x, 2.0 * sv.y);
-          sv = cfma(hrow[j], omx2[j], sv);
-          if (i == j) { sv.x += 2.0 * qv[j].x; sv.y += 2.0 * qv[j].y; }
-          tl[a][c] = sv;
+        for (int a = 0; a < RA; ++a) {
+          if (a >= nra) continue;
+          const int i = warp + 16 * a;
+#pragma unroll
+          for (int c = 0; c < NCOL; ++c) {
+            const int j = min(lane + 32 * c, ff - 1);
+            cplx sv = cmul(tl[a][c], XQ[j]);
+            sv = make_double2(2.0 * sv.x, 2.0 * sv.y);
+            sv = cfma(h0[a * hstep + j], omx2[j], sv);
+            if (i == j) { sv.x += 2.0 * qv[j].x; sv.y += 2.0 * qv[j].y; }
+            tl[a][c] = sv;
+          }
         }
       }
       RK_PHASE(18);
       for (int t = tid; t < ff; t += NT) bvec[t] = cscale(r0, wr[2 * ff + t]);
-      ctile_lu_implicit<RA, NCOL>(tl, rowk, colk, magk, bvec, ipiv, ff, warp, lane);
+      { const CTile<RA, NCOL> R_ = ctile_lu_call<RA, NCOL>(ctile_pack<RA, NCOL>(tl), rowk, colk, yv, magk, reinterpret_cast<double*>(dv), bvec, ipiv, ff, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
+      RK_PHASE(11);
       // rows out in pivot order: P_r S = L U in the usual layout; b' = P_r b
       int* pos = reinterpret_cast<int*>(magk);
       for (int k = tid; k < ff; k += NT) { pos[ipiv[k]] = k; colk[k] = bvec[ipiv[k]]; }
@@ -449,9 +644,12 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     }
     }
     __syncthreads();
+    RK_PHASE(12);
+    for (int t = tid; t < ff; t += NT) colk[t] = cinv(Sm[t * ld + t]);   // 1 / U_kk, also used by the U^H solve of the reverse sweep
+    __syncthreads();
     if (warp == 0) {   // back substitution U c+ = b'
       for (int k = ff - 1; k >= 0; --k) {
-        cplx xk = cmul(bvec[k], cinv(Sm[k * ld + k]));
+        cplx xk = cmul(bvec[k], colk[k]);
         __syncwarp();
         if (lane == 0) bvec[k] = xk;
         for (int i = lane; i < k; i += 32) bvec[i] = cfnma(Sm[i * ld + k], xk, bvec[i]);
@@ -519,7 +717,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     if (warp == 0) {
       // U^H w = c (forward), L^H v = w (backward, unit diagonal), bb = P_r^T v (swaps in reverse order)
       for (int k = 0; k < ff; ++k) {
-        cplx wk = cmul(rowk[k], cinv(cconj(Sm[k * ld + k])));
+        cplx wk = cmul(rowk[k], cconj(colk[k]));
         __syncwarp();
         if (lane == 0) rowk[k] = wk;
         for (int i = k + 1 + lane; i < ff; i += 32) rowk[i] = cfnma(cconj(Sm[k * ld + i]), wk, rowk[i]);
@@ -608,19 +806,23 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     }
     __syncthreads();
     RK_PHASE(21);
-    // six products H x -> Lf columns (Re, -Im);  H_I = Hq + Q
-    for (int v = 0; v < 6; ++v) {
-      const cplx* M = (v < 2) ? Hq : HII;
-      const cplx* x = v_in + (size_t)v * ff;
-      for (int i = warp; i < ff; i += NW) {
-        cplx s = make_double2(0.0, 0.0);
-        for (int j = lane; j < ff; j += 32) s = cfma(M[(size_t)i * ff + j], x[j], s);
-        s = warp_sum(s);
-        if (lane == 0) {
-          if (v < 2) s = cfma(qv[i], x[i], s);
-          Lf[i * PIRL_GRAD_RANK + 2 * v] = s.x;
-          Lf[i * PIRL_GRAD_RANK + 2 * v + 1] = -s.y;
-        }
+    // six products H x -> Lf columns (Re, -Im);  H_I = Hq + Q.  One pass over the rows for all six vectors.
+    for (int i = warp; i < ff; i += NW) {
+      cplx s6[6];
+#pragma unroll
+      for (int v = 0; v < 6; ++v) s6[v] = make_double2(0.0, 0.0);
+      for (int j = lane; j < ff; j += 32) {
+        const cplx m1 = Hq[(size_t)i * ff + j], m2 = HII[(size_t)i * ff + j];
+#pragma unroll
+        for (int v = 0; v < 6; ++v) s6[v] = cfma(v < 2 ? m1 : m2, v_in[(size_t)v * ff + j], s6[v]);
+      }
+#pragma unroll
+      for (int v = 0; v < 6; ++v) s6[v] = warp_sum(s6[v]);
+      if (lane == 0) {
+        s6[0] = cfma(qv[i], v_in[i], s6[0]);
+        s6[1] = cfma(qv[i], v_in[ff + i], s6[1]);
+#pragma unroll
+        for (int v = 0; v < 6; ++v) { Lf[i * PIRL_GRAD_RANK + 2 * v] = s6[v].x; Lf[i * PIRL_GRAD_RANK + 2 * v + 1] = -s6[v].y; }
       }
     }
     RK_PHASE(22);
