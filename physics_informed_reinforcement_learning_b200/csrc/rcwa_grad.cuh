@@ -142,13 +142,17 @@ __device__ __forceinline__ void ctile_gj_inverse(cplx (&t)[RA][CC], cplx* rc0, c
         const int j = lane + 32 * c;
         rv[c] = (j < ff) ? ((j == k) ? make_double2(1.0 + piv.x, piv.y) : rowk[j]) : make_double2(0.0, 0.0);
       }
+      // (loads first, see the S product in g_tail; row slots past the matrix work on a clamped row, their tile is never read)
+      cplx ck[RA];
+#pragma unroll
+      for (int a = 0; a < RA; ++a) ck[a] = colk[min(w + 16 * a, ff - 1)];
 #pragma unroll
       for (int a = 0; a < RA; ++a) {
-        if (a >= nra) continue;
+        if (a == RA - 1 && nra < RA) continue;
         const int i = w + 16 * a;
-        const cplx cv = (i == k) ? make_double2(p.x - 1.0, p.y) : cscale(cmul(colk[i], p), -1.0);
+        const cplx cv = (i == k) ? make_double2(1.0 - p.x, -p.y) : cmul(ck[a], p);     // minus the usual multiplier
 #pragma unroll
-        for (int c = 0; c < CC; ++c) t[a][c] = cfma(cv, rv[c], t[a][c]);
+        for (int c = 0; c < CC; ++c) t[a][c] = cfnma(cv, rv[c], t[a][c]);
       }
       if (k1 < ff) {
         if (kk < 15) ctile_publish<RA, CC>(t, (k & 1) ? rc0 : rc2, (k & 1) ? rc1 : rc3, k1, KB, ff, w, lane);
@@ -221,11 +225,14 @@ __device__ __forceinline__ void ctile_lu_implicit(cplx (&t)[RA][CC], cplx* rowk,
       cplx rv[CC];
 #pragma unroll
       for (int c = 0; c < CC; ++c) { const int j = lane + 32 * c; rv[c] = (j < ff && j > k) ? rowk[j] : make_double2(0.0, 0.0); }
+      cplx ck[RA];
+#pragma unroll
+      for (int a = 0; a < RA; ++a) ck[a] = colk[min(w + 16 * a, ff - 1)];
 #pragma unroll
       for (int a = 0; a < RA; ++a) {
         if ((used >> a) & 1u) continue;          // warp-uniform
         const int i = w + 16 * a;
-        const cplx f = cmul(colk[i], pinv);
+        const cplx f = cmul(ck[a], pinv);
 #pragma unroll
         for (int c = 0; c < CC; ++c) t[a][c] = cfnma(f, rv[c], t[a][c]);
         if (lane == kk) t[a][KC] = f;
@@ -246,15 +253,26 @@ __device__ __forceinline__ void ctile_lu_implicit(cplx (&t)[RA][CC], cplx* rowk,
 template <int RA, int CC>
 struct CTile { cplx v[RA][CC]; };
 
+// Shared-memory operands of the non-inlined calls travel as offsets (in doubles) from the dynamic shared array: a pointer
+// argument would be generic and every load in the callee a generic load.
+template <class T>
+__device__ __forceinline__ T* smem_at(int off) {
+  extern __shared__ __align__(16) double sm[];
+  return reinterpret_cast<T*>(sm + off);
+}
+__device__ __forceinline__ int smem_off(const void* p) {
+  extern __shared__ __align__(16) double sm[];
+  return (int)(reinterpret_cast<const double*>(p) - sm);
+}
+
 template <int RA, int CC>
-__device__ __noinline__ CTile<RA, CC> ctile_gj_call(CTile<RA, CC> T, cplx* rc0, cplx* rc1, cplx* rc2, cplx* rc3, cplx* pslot, int ff,
-                                                    int w, int lane) {
+__device__ __noinline__ CTile<RA, CC> ctile_gj_call(CTile<RA, CC> T, int rc0, int rc1, int rc2, int rc3, int pslot, int ff, int w, int lane) {
   cplx t[RA][CC];   // explicit register copy: the by-value parameter itself stays in param (local) memory
 #pragma unroll
   for (int a = 0; a < RA; ++a)
 #pragma unroll
     for (int c = 0; c < CC; ++c) t[a][c] = T.v[a][c];
-  ctile_gj_inverse<RA, CC>(t, rc0, rc1, rc2, rc3, pslot, ff, w, lane);
+  ctile_gj_inverse<RA, CC>(t, smem_at<cplx>(rc0), smem_at<cplx>(rc1), smem_at<cplx>(rc2), smem_at<cplx>(rc3), smem_at<cplx>(pslot), ff, w, lane);
   CTile<RA, CC> R;
 #pragma unroll
   for (int a = 0; a < RA; ++a)
@@ -263,14 +281,105 @@ __device__ __noinline__ CTile<RA, CC> ctile_gj_call(CTile<RA, CC> T, cplx* rc0, 
   return R;
 }
 template <int RA, int CC>
-__device__ __noinline__ CTile<RA, CC> ctile_lu_call(CTile<RA, CC> T, cplx* rowk, cplx* colk0, cplx* colk1, double* magk0, double* magk1,
-                                                    cplx* bvec, int* rperm, int ff, int w, int lane) {
+__device__ __noinline__ CTile<RA, CC> ctile_lu_call(CTile<RA, CC> T, int rowk, int colk0, int colk1, int magk0, int magk1, int bvec, int rperm,
+                                                    int ff, int w, int lane) {
   cplx t[RA][CC];
 #pragma unroll
   for (int a = 0; a < RA; ++a)
 #pragma unroll
     for (int c = 0; c < CC; ++c) t[a][c] = T.v[a][c];
-  ctile_lu_implicit<RA, CC>(t, rowk, colk0, colk1, magk0, magk1, bvec, rperm, ff, w, lane);
+  ctile_lu_implicit<RA, CC>(t, smem_at<cplx>(rowk), smem_at<cplx>(colk0), smem_at<cplx>(colk1), smem_at<double>(magk0), smem_at<double>(magk1),
+                            smem_at<cplx>(bvec), smem_at<int>(rperm), ff, w, lane);
+  CTile<RA, CC> R;
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) R.v[a][c] = t[a][c];
+  return R;
+}
+
+// W^T Re(D_I) W and W^T Re(D_II) W (real parts of H_I, H_II) for the rows / columns of this thread: harmonic index outermost,
+// all loads of a step issued before its multiply-adds; row slots past the matrix read a clamped row (never used afterwards)
+template <int RA, int CC>
+struct RTile2 { double a[RA][CC], b[RA][CC]; };
+
+template <int RA, int CC>
+__device__ __noinline__ RTile2<RA, CC> rtile_wdw_call(int oW, int oDI, int oDII, int ff, int ld, int w, int lane) {
+  const double* Wr = smem_at<double>(oW);
+  const cplx* DI = smem_at<cplx>(oDI);
+  const cplx* DII = smem_at<cplx>(oDII);
+  double aI[RA][CC], aII[RA][CC];
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) { aI[a][c] = 0.0; aII[a][c] = 0.0; }
+  int rix[RA], cix[CC];
+#pragma unroll
+  for (int a = 0; a < RA; ++a) rix[a] = min(w + 16 * a, ff - 1);
+#pragma unroll
+  for (int c = 0; c < CC; ++c) cix[c] = min(lane + 32 * c, ff - 1);
+  const bool last_slot = w + 16 * (RA - 1) < ff;
+#pragma unroll 2
+  for (int m = 0; m < ff; ++m) {
+    const double d1 = DI[m].x, d2 = DII[m].x;
+    const double* wrow = Wr + m * ld;
+    double wj[CC], wi[RA];
+#pragma unroll
+    for (int c = 0; c < CC; ++c) wj[c] = wrow[cix[c]];
+#pragma unroll
+    for (int a = 0; a < RA; ++a) wi[a] = wrow[rix[a]];
+#pragma unroll
+    for (int a = 0; a < RA - 1; ++a) {
+      const double w1 = wi[a] * d1, w2 = wi[a] * d2;
+#pragma unroll
+      for (int c = 0; c < CC; ++c) { aI[a][c] = fma(w1, wj[c], aI[a][c]); aII[a][c] = fma(w2, wj[c], aII[a][c]); }
+    }
+    if (last_slot) {
+      const double w1 = wi[RA - 1] * d1, w2 = wi[RA - 1] * d2;
+#pragma unroll
+      for (int c = 0; c < CC; ++c) { aI[RA - 1][c] = fma(w1, wj[c], aI[RA - 1][c]); aII[RA - 1][c] = fma(w2, wj[c], aII[RA - 1][c]); }
+    }
+  }
+  RTile2<RA, CC> R;
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) { R.a[a][c] = aI[a][c]; R.b[a][c] = aII[a][c]; }
+  return R;
+}
+
+// (A P) for the rows / columns of this thread, A = Hq X and P complex [ff][ld] in shared memory
+template <int RA, int CC>
+__device__ __noinline__ CTile<RA, CC> ctile_ap_call(int oA, int oP, int ff, int ld, int w, int lane) {
+  const cplx* Am = smem_at<cplx>(oA);
+  const cplx* Pm = smem_at<cplx>(oP);
+  cplx t[RA][CC];
+#pragma unroll
+  for (int a = 0; a < RA; ++a)
+#pragma unroll
+    for (int c = 0; c < CC; ++c) t[a][c] = make_double2(0.0, 0.0);
+  int roff[RA], cix[CC];
+#pragma unroll
+  for (int a = 0; a < RA; ++a) roff[a] = min(w + 16 * a, ff - 1) * ld;
+#pragma unroll
+  for (int c = 0; c < CC; ++c) cix[c] = min(lane + 32 * c, ff - 1);
+  const bool last_slot = w + 16 * (RA - 1) < ff;
+#pragma unroll 1
+  for (int k = 0; k < ff; ++k) {
+    cplx pk[CC], f[RA];
+#pragma unroll
+    for (int c = 0; c < CC; ++c) pk[c] = Pm[k * ld + cix[c]];
+#pragma unroll
+    for (int a = 0; a < RA; ++a) f[a] = Am[roff[a] + k];
+#pragma unroll
+    for (int a = 0; a < RA - 1; ++a)
+#pragma unroll
+      for (int c = 0; c < CC; ++c) t[a][c] = cfma(f[a], pk[c], t[a][c]);
+    if (last_slot) {
+#pragma unroll
+      for (int c = 0; c < CC; ++c) t[RA - 1][c] = cfma(f[RA - 1], pk[c], t[RA - 1][c]);
+    }
+  }
   CTile<RA, CC> R;
 #pragma unroll
   for (int a = 0; a < RA; ++a)
@@ -328,8 +437,10 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
   cplx* Hq = reinterpret_cast<cplx*>(scr);          // [ff][ff] global (L2 resident)
   cplx* HII = Hq + (size_t)ff * ff;
   cplx* spill = HII + (size_t)ff * ff;
-  cplx* Pm = (G.smem_mats >= 1) ? reinterpret_cast<cplx*>(mat0) : spill;
-  cplx* Sm = (G.smem_mats >= 2) ? reinterpret_cast<cplx*>(mat0) + csz : spill + csz;
+  // the register-tile variant is only launched when both matrices fit in shared memory: plain shared pointers then (a pointer
+  // that may be shared or global compiles to generic loads with 64-bit address arithmetic in the inner loops)
+  cplx* Pm = (REG || G.smem_mats >= 1) ? reinterpret_cast<cplx*>(mat0) : spill;
+  cplx* Sm = (REG || G.smem_mats >= 2) ? reinterpret_cast<cplx*>(mat0) + csz : spill + csz;
   double* Wr = reinterpret_cast<double*>(Sm);
   cplx* gv = spill + 2 * csz;                       // 16 global vectors
   cplx* v_ell = gv;           cplx* v_x = gv + ff;       cplx* v_yb = gv + 2 * ff;  cplx* v_qb = gv + 3 * ff;
@@ -390,28 +501,10 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
         if (lane == 0) { lstI[0] = c1; lstII[0] = c2; }
       }
       {
-        double aI[RA][NCOL], aII[RA][NCOL];
-#pragma unroll
-        for (int a = 0; a < RA; ++a)
-#pragma unroll
-          for (int c = 0; c < NCOL; ++c) { aI[a][c] = 0.0; aII[a][c] = 0.0; }
         const int nra = (ff - warp + 15) >> 4;             // row slots of this warp that hold a row (warp-uniform)
-#pragma unroll 1
-        for (int m = 0; m < ff; ++m) {
-          const double d1 = DI[m].x, d2 = DII[m].x;
-          const double* wrow = Wr + m * ld;
-          double wj[NCOL];
-#pragma unroll
-          for (int c = 0; c < NCOL; ++c) wj[c] = wrow[min(lane + 32 * c, ff - 1)];
-#pragma unroll
-          for (int a = 0; a < RA; ++a) {
-            if (a >= nra) continue;
-            const double wi = wrow[warp + 16 * a];
-            const double w1 = wi * d1, w2 = wi * d2;
-#pragma unroll
-            for (int c = 0; c < NCOL; ++c) { aI[a][c] = fma(w1, wj[c], aI[a][c]); aII[a][c] = fma(w2, wj[c], aII[a][c]); }
-          }
-        }
+        const RTile2<RA, NCOL> R2_ = rtile_wdw_call<RA, NCOL>(smem_off(Wr), smem_off(DI), smem_off(DII), ff, ld, warp, lane);
+        const double (&aI)[RA][NCOL] = R2_.a;
+        const double (&aII)[RA][NCOL] = R2_.b;
         RK_PHASE(9);
         __syncthreads();                                   // lists visible
         // imaginary parts: sum over the propagating harmonics of Im(D_m) w_m w_m^T, first medium I (-> Hq), then II
@@ -465,7 +558,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
         }
       }
       RK_PHASE(16);
-      { const CTile<RA, NCOL> R_ = ctile_gj_call<RA, NCOL>(ctile_pack<RA, NCOL>(tl), rowk, colk, yv, dv, red, ff, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
+      { const CTile<RA, NCOL> R_ = ctile_gj_call<RA, NCOL>(ctile_pack<RA, NCOL>(tl), smem_off(rowk), smem_off(colk), smem_off(yv), smem_off(dv), smem_off(red), ff, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
       ctile_store<RA, NCOL>(tl, Pm, ld, ff, warp, lane);
       // Hq X staged in S's storage (W is dead, the LU rows are written back much later)
       for (int i = warp; i < ff; i += NW)
@@ -474,29 +567,11 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       RK_PHASE(17);
       // ---- S = Hq (I - X^2) + 2Q + 2 (Hq X) P (X Q) -> register tile ----
       // k outermost: per k three shared-memory loads of P and six broadcast loads of Hq X feed 18 complex multiply-adds
-#pragma unroll
-      for (int a = 0; a < RA; ++a)
-#pragma unroll
-        for (int c = 0; c < NCOL; ++c) tl[a][c] = make_double2(0.0, 0.0);
       {
         const int nra = (ff - warp + 15) >> 4;
         const cplx* h0 = Hq + (size_t)warp * ff;           // row warp + 16 a starts at h0 + a * hstep
         const int hstep = 16 * ff;
-        const cplx* a0 = Sm + warp * ld;
-        const int astep = 16 * ld;
-#pragma unroll 1
-        for (int k = 0; k < ff; ++k) {
-          cplx pk[NCOL];
-#pragma unroll
-          for (int c = 0; c < NCOL; ++c) pk[c] = Pm[k * ld + min(lane + 32 * c, ff - 1)];
-#pragma unroll
-          for (int a = 0; a < RA; ++a) {
-            if (a >= nra) continue;                        // warp-uniform
-            const cplx f = a0[a * astep + k];
-#pragma unroll
-            for (int c = 0; c < NCOL; ++c) tl[a][c] = cfma(f, pk[c], tl[a][c]);
-          }
-        }
+        { const CTile<RA, NCOL> R_ = ctile_ap_call<RA, NCOL>(smem_off(Sm), smem_off(Pm), ff, ld, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
         RK_PHASE(10);
 #pragma unroll
         for (int a = 0; a < RA; ++a) {
@@ -515,7 +590,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       }
       RK_PHASE(18);
       for (int t = tid; t < ff; t += NT) bvec[t] = cscale(r0, wr[2 * ff + t]);
-      { const CTile<RA, NCOL> R_ = ctile_lu_call<RA, NCOL>(ctile_pack<RA, NCOL>(tl), rowk, colk, yv, magk, reinterpret_cast<double*>(dv), bvec, ipiv, ff, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
+      { const CTile<RA, NCOL> R_ = ctile_lu_call<RA, NCOL>(ctile_pack<RA, NCOL>(tl), smem_off(rowk), smem_off(colk), smem_off(yv), smem_off(magk), smem_off(dv), smem_off(bvec), smem_off(ipiv), ff, warp, lane); ctile_unpack<RA, NCOL>(tl, R_); }
       RK_PHASE(11);
       // rows out in pivot order: P_r S = L U in the usual layout; b' = P_r b
       int* pos = reinterpret_cast<int*>(magk);
@@ -920,7 +995,7 @@ __device__ __forceinline__ void toeplitz_adjoint_add(int i, int j, int N, double
 // ===================================================================================================
 // g_eigback : reverse sweep through the generalised symmetric eigenproblem, B, E^-1, the Toeplitz maps and the DFT
 // ===================================================================================================
-template <int NT>
+template <int NT, bool SM_ALL>
 __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
   static_assert(NT == 256, "cta_gemm assumes 16 x 16 threads");
   extern __shared__ __align__(16) double sm[];
@@ -941,7 +1016,7 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
   const size_t msz = (size_t)ff * ld;
   double* scr = G.gscratch + (size_t)blockIdx.x * G.gstride;
   double* M[4];
-  for (int m = 0; m < 4; ++m) M[m] = (m < G.smem_mats) ? mat0 + m * msz : scr + m * msz;
+  for (int m = 0; m < 4; ++m) M[m] = (SM_ALL || m < G.smem_mats) ? mat0 + m * msz : scr + m * msz;   // SM_ALL: plain shared pointers
   double *M0 = M[0], *M1 = M[1], *M2 = M[2], *M3 = M[3];
 
   for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
