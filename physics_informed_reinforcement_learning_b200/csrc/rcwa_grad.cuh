@@ -196,6 +196,8 @@ __device__ __forceinline__ void ctile_lu_implicit(cplx (&t)[RA][CC], cplx* rowk,
       const cplx* colk = (k & 1) ? colk1 : colk0;
       const double* magk = (k & 1) ? magk1 : magk0;
       // every warp finds the same pivot (largest |re| + |im| among the unused rows, lowest row on ties)
+      // (tried: integer keys with the row packed into the low bits and the reciprocal of each lane's best candidate computed
+      // under the shuffle rounds -- 15 % slower per step than this plain search)
       double best = -2.0; int pv = 0;
       for (int i = lane; i < ff; i += 32) { const double m = magk[i]; if (m > best) { best = m; pv = i; } }
 #pragma unroll
@@ -403,6 +405,42 @@ __device__ __forceinline__ void ctile_unpack(cplx (&t)[RA][CC], const CTile<RA, 
   for (int a = 0; a < RA; ++a)
 #pragma unroll
     for (int c = 0; c < CC; ++c) t[a][c] = T.v[a][c];
+}
+
+// Triangular solve by one warp with the vector in registers (lane l holds x[l + 32 c]): per step one shuffle broadcast of
+// x_k, one complex multiply and one multiply-add sit on the dependency chain; the matrix elements of the step are loaded
+// ahead of it.  DESC: k runs downwards and rows i < k are updated (else upwards, i > k).  ROWACC: the element that couples
+// x_i to x_k is M[k][i] (else M[i][k]); CONJ: its conjugate (and conj(dinv)); UNIT: unit diagonal.
+template <int CC, bool DESC, bool ROWACC, bool CONJ, bool UNIT>
+__device__ __forceinline__ void warp_trisolve(cplx (&x)[CC], const cplx* M, int ld, const cplx* dinv, int ff, int lane) {
+#pragma unroll
+  for (int KC0 = 0; KC0 < CC; ++KC0) {
+    const int KC = DESC ? CC - 1 - KC0 : KC0;
+#pragma unroll 1
+    for (int kk0 = 0; kk0 < 32; ++kk0) {
+      const int kk = DESC ? 31 - kk0 : kk0;
+      const int k = 32 * KC + kk;
+      if (k >= ff) { if (DESC) continue; else break; }
+      cplx m[CC];
+#pragma unroll
+      for (int c = 0; c < CC; ++c) {
+        const int i = min(lane + 32 * c, ff - 1);
+        m[c] = ROWACC ? M[k * ld + i] : M[i * ld + k];
+      }
+      cplx xk = make_double2(__shfl_sync(0xffffffffu, x[KC].x, kk), __shfl_sync(0xffffffffu, x[KC].y, kk));
+      if (!UNIT) {
+        const cplx d = dinv[k];
+        xk = cmul(xk, CONJ ? cconj(d) : d);
+        if (lane == kk) x[KC] = xk;
+      }
+#pragma unroll
+      for (int c = 0; c < CC; ++c) {
+        const int i = lane + 32 * c;
+        const bool on = DESC ? (i < k) : (i > k && i < ff);
+        if (on) x[c] = cfnma(CONJ ? cconj(m[c]) : m[c], xk, x[c]);
+      }
+    }
+  }
 }
 
 // ===================================================================================================
@@ -723,13 +761,12 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     for (int t = tid; t < ff; t += NT) colk[t] = cinv(Sm[t * ld + t]);   // 1 / U_kk, also used by the U^H solve of the reverse sweep
     __syncthreads();
     if (warp == 0) {   // back substitution U c+ = b'
-      for (int k = ff - 1; k >= 0; --k) {
-        cplx xk = cmul(bvec[k], colk[k]);
-        __syncwarp();
-        if (lane == 0) bvec[k] = xk;
-        for (int i = lane; i < k; i += 32) bvec[i] = cfnma(Sm[i * ld + k], xk, bvec[i]);
-        __syncwarp();
-      }
+      cplx xr[NCOL];
+#pragma unroll
+      for (int c = 0; c < NCOL; ++c) xr[c] = bvec[min(lane + 32 * c, ff - 1)];
+      warp_trisolve<NCOL, true, false, false, false>(xr, Sm, ld, colk, ff, lane);
+#pragma unroll
+      for (int c = 0; c < NCOL; ++c) if (lane + 32 * c < ff) bvec[lane + 32 * c] = xr[c];
     }
     __syncthreads();
     // ---- y = Q X c+,  d = 2 P y ----
@@ -791,17 +828,14 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     __syncthreads();
     if (warp == 0) {
       // U^H w = c (forward), L^H v = w (backward, unit diagonal), bb = P_r^T v (swaps in reverse order)
-      for (int k = 0; k < ff; ++k) {
-        cplx wk = cmul(rowk[k], cconj(colk[k]));
-        __syncwarp();
-        if (lane == 0) rowk[k] = wk;
-        for (int i = k + 1 + lane; i < ff; i += 32) rowk[i] = cfnma(cconj(Sm[k * ld + i]), wk, rowk[i]);
-        __syncwarp();
-      }
-      for (int k = ff - 1; k >= 1; --k) {
-        const cplx vk = rowk[k];
-        __syncwarp();
-        for (int i = lane; i < k; i += 32) rowk[i] = cfnma(cconj(Sm[k * ld + i]), vk, rowk[i]);
+      {
+        cplx xr[NCOL];
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) xr[c] = rowk[min(lane + 32 * c, ff - 1)];
+        warp_trisolve<NCOL, false, true, true, false>(xr, Sm, ld, colk, ff, lane);
+        warp_trisolve<NCOL, true, true, true, true>(xr, Sm, ld, colk, ff, lane);
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) if (lane + 32 * c < ff) rowk[lane + 32 * c] = xr[c];
         __syncwarp();
       }
       if constexpr (REG) {        // bb[rperm[k]] = v[k]
