@@ -62,6 +62,21 @@ def test_large_order_against_fresh_oracle_fd(pkg):
     be.close()
 
 
+@pytest.mark.parametrize("order", [7, 45])
+def test_every_kernel_variant_against_oracle_fd(pkg, order):
+    """Orders 40 / 60 / 100 are covered above; order 7 (ff = 15) runs the register-tile g_tail with most row slots empty,
+    order 45 (ff = 91) the shared-memory g_tail with one matrix spilled to L2 scratch and g_eigback with generic pointers."""
+    from oracle import rcwa_oracle
+    pat = np.random.default_rng(order).choice([-1.0, 1.0], 128)
+    be = pkg.RCWABatch(128, order, max_batch=4, device=0)
+    eff, grad, st = be.evaluate_grad_host(pat[None, :], 1000.0, 55.0, 300.0)
+    idx = [0, 31, 64, 127]
+    fd = rcwa_oracle.fd_gradient(pat, idx, wavelength=1000.0, angle=55.0, order=order, thickness=300.0)
+    assert st[0] == 0
+    assert _close(grad[0, idx], fd).all(), (grad[0, idx], fd)
+    be.close()
+
+
 def test_uniform_and_degenerate_patterns(pkg, torch_mod):
     """Uniform slabs have exactly degenerate cos/sin mode pairs: the degenerate pairs must drop out, not produce inf/nan."""
     from oracle import rcwa_oracle
