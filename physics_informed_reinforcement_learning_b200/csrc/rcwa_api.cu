@@ -78,6 +78,7 @@ struct pirl_handle {
   double* hd_grad = nullptr; int64_t hd_grad_cap = 0;
   // per-kernel timing (pirl_rcwa_set_stage_timing)
   bool timing = false;
+  bool sync_launch = false; int sync_fail_stage = -1; cudaError_t sync_err = cudaSuccess;   // PIRL_SYNC_LAUNCH=1: synchronise after every kernel
   std::vector<cudaEvent_t> ev_free;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
 };
@@ -120,6 +121,10 @@ struct StageTimer {   // brackets one kernel launch with events when timing is o
   }
   ~StageTimer() {
     if (h->timing) { cudaEventRecord(b, st); h->ev_pending.push_back({stage, {a, b}}); }
+    if (h->sync_launch && h->sync_fail_stage < 0) {   // diagnostic: name the first kernel that faults
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { h->sync_fail_stage = stage; h->sync_err = e; }
+    }
   }
 };
 
@@ -247,7 +252,8 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     const size_t abudget = budget - 2 * (size_t)(256 + 2 * 4) * 4 * sizeof(cplx);   // static rotation buffers
     h->apply_smem = apply_bytes(h->apply_rows, h->apply_k);
     if (h->apply_smem > abudget) { h->apply_rows = 32; h->apply_smem = apply_bytes(32, h->apply_k); }
-    if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4, 81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
+    if (h->apply_rows == 96 && ff <= 81) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4, 81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
+    else if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4, 96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
     else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
     else CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
     h->ql_smem = (size_t)2 * ff * 32 * 8;
@@ -296,6 +302,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
   CUDA_TRY(max_carveout(rk_front<Cfg81>)); CUDA_TRY(max_carveout(rk_tail<Cfg81T, kTailMmax>));
+  h->sync_launch = getenv("PIRL_SYNC_LAUNCH") != nullptr;
   if (getenv("PIRL_TRACE")) {
     CUDA_TRY(dmalloc(&h->trace, 1 + 4 * (size_t)PIRL_TRACE_CAP));
     CUDA_TRY(cudaMemset(h->trace, 0, sizeof(unsigned long long)));
@@ -405,7 +412,9 @@ static void launch_ql(pirl_handle* h, const KParams& P, cudaStream_t st) {
 static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
     StageTimer t(h, 3, st);
     dim3 g(P.B, (h->ff + h->apply_rows - 1) / h->apply_rows);
-    if (h->apply_rows == 96) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
+    // (the third template argument sizes the static rotation buffers: ff <= 81 keeps three CTAs per SM at the headline size)
+    if (h->apply_rows == 96 && h->ff <= 81) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
+    else if (h->apply_rows == 96) k_apply<96, 4, 96><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 64) k_apply<64, 2, 256><<<g, 64, h->apply_smem, st>>>(P);
     else k_apply<32, 2, 256><<<g, 32, h->apply_smem, st>>>(P);
     h->launches += 1;
@@ -541,6 +550,8 @@ static int launch_chunk(pirl_handle* h, KParams P, int Bc, cudaStream_t st, cons
     }
   }
   h->last_chunk = Bc;
+  if (h->sync_fail_stage >= 0)
+    return fail((int)h->sync_err, std::string("kernel ") + kStageNames[h->sync_fail_stage] + ": " + cudaGetErrorString(h->sync_err));
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -103,7 +103,7 @@ def test_sweep_fixture_per_structure_parameters(golden_dir, pkg, torch_mod):
     be.close()
 
 
-@pytest.mark.parametrize("n_cells,order,count", [(256, 40, 48), (64, 8, 32), (256, 60, 12), (512, 100, 3), (100, 17, 8)])
+@pytest.mark.parametrize("n_cells,order,count", [(256, 40, 48), (64, 8, 32), (256, 60, 12), (512, 100, 3), (100, 17, 8), (128, 45, 6), (128, 47, 4), (128, 41, 4)])
 def test_against_oracle_on_seeded_inputs(pkg, n_cells, order, count):
     from oracle import rcwa_oracle as O
     rng = np.random.default_rng(1000 + n_cells + order)
