@@ -187,7 +187,9 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     }
     const long double R = 4.0L * N + 2.0L, M = R * nc;
     for (int k = 0; k <= 2 * N; ++k) {
-      std::complex<long double> d(1.0L, 0.0L);
+      // zero-order hold factor of the up-sampled pattern: 1 at k = 0, exactly 0 at the other multiples of n_cells
+      // (harmonics that alias onto the mean: they occur when 2 * order >= n_cells)
+      std::complex<long double> d(k == 0 ? 1.0L : 0.0L, 0.0L);
       if (k % nc != 0) {
         std::complex<long double> num = 1.0L - std::polar(1.0L, -2.0L * PI * k / nc);
         std::complex<long double> den = R * (1.0L - std::polar(1.0L, -2.0L * PI * k / M));

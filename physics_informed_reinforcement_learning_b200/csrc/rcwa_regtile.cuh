@@ -117,9 +117,10 @@ __global__ void __maxnreg__(C::MAXREG) rk_front(KParams P) {
     for (int k = tid; k <= 2 * N; k += NT) {
       double sx = 0.0, sy = 0.0;
       int idx = 0;
+      const int km = k % nc;                     // harmonics >= n_cells alias (2 * order >= n_cells)
       for (int p = 0; p < nc; ++p) {
         if (su[p]) { const cplx w = twS[idx]; sx += w.x; sy += w.y; }
-        idx += k; if (idx >= nc) idx -= nc;
+        idx += km; if (idx >= nc) idx -= nc;
       }
       const cplx d = __ldg(&P.Dk[k]);
       cre[k] = sx * d.x - sy * d.y;

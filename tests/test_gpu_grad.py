@@ -62,7 +62,7 @@ def test_large_order_against_fresh_oracle_fd(pkg):
     be.close()
 
 
-@pytest.mark.parametrize("order", [7, 45])
+@pytest.mark.parametrize("order", [1, 2, 7, 45, 48, 49, 64, 70])
 def test_every_kernel_variant_against_oracle_fd(pkg, order):
     """Orders 40 / 60 / 100 are covered above; order 7 (ff = 15) runs the register-tile g_tail with most row slots empty,
     order 45 (ff = 91) the shared-memory g_tail with one matrix spilled to L2 scratch and g_eigback with generic pointers."""

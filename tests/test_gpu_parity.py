@@ -124,6 +124,25 @@ def test_against_oracle_on_seeded_inputs(pkg, n_cells, order, count):
     be.close()
 
 
+def test_every_order_against_oracle(pkg):
+    """One handle per order (every order up to 70, every third up to the maximum 126): crosses every kernel-variant boundary of
+    the launch plans (k_apply row / sweep variants at ff = 81 / 96, k_tail column variants at 96 / 128, the register-tile sizes
+    81 and 121) and, with 96 cells, the orders whose harmonics alias (2 * order >= n_cells), two structures each."""
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(4242)
+    n_cells, wl, ang, thick = 96, 1050.0, 58.0, 310.0
+    worst = 0.0
+    for order in list(range(1, 71)) + list(range(72, 127, 3)):
+        pats = np.stack([rng.choice([-1, 1], n_cells), np.repeat(rng.choice([-1, 1], n_cells // 8), 8)]).astype(np.int8)
+        be = pkg.RCWABatch(n_cells, order, max_batch=4)
+        eff, st = be.evaluate_host(pats, wl, ang, thick), None
+        for i in range(2):
+            r = O.evaluate(pats[i].astype(np.float64), wl, ang, order, thick)
+            worst = max(worst, abs(eff[i] - r.eff))
+            assert abs(eff[i] - r.eff) <= TIGHT, (order, i, eff[i], r.eff)
+        be.close()
+
+
 def test_other_wavelengths_angles_thickness_vs_oracle(pkg):
     from oracle import rcwa_oracle as O
     rng = np.random.default_rng(77)
