@@ -261,7 +261,10 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
-  if (ff == Cfg81::FF && !getenv("PIRL_NO_REGTILE")) {
+  // the register-tile front kernels keep the twiddle table and the pattern of n_cells entries in shared memory: very long
+  // patterns (about 10^4 cells and more) do not fit and run the generic kernels
+  const size_t rk_budget = h->smem_optin - 1024;
+  if (ff == Cfg81::FF && !getenv("PIRL_NO_REGTILE") && (size_t)FrontSmem<Cfg81>::doubles(nc) * 8 <= rk_budget) {
     h->regtile = true;
     h->rk_front_smem = (size_t)FrontSmem<Cfg81>::doubles(nc) * 8;
     CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
@@ -284,7 +287,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->rk_tail2_grid = h->sm_count * per_sm;
     h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }
-  if (ff == Cfg121::FFR && !getenv("PIRL_NO_REGTILE")) {
+  if (ff == Cfg121::FFR && !getenv("PIRL_NO_REGTILE") && (size_t)FrontSmem<Cfg121>::doubles(nc) * 8 <= rk_budget) {
     h->regfront121 = true;
     h->rk_front_smem = (size_t)FrontSmem<Cfg121>::doubles(nc) * 8;
     CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg121>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
@@ -301,7 +304,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->rk_tail2_grid = h->sm_count * per_sm;
   }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
-  CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
+  CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<96, 4, 96>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
   CUDA_TRY(max_carveout(rk_front<Cfg81>)); CUDA_TRY(max_carveout(rk_tail<Cfg81T, kTailMmax>));
   h->sync_launch = getenv("PIRL_SYNC_LAUNCH") != nullptr;

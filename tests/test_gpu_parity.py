@@ -143,6 +143,34 @@ def test_every_order_against_oracle(pkg):
         be.close()
 
 
+@pytest.mark.parametrize("n_cells", [2, 3, 7, 255, 257, 1000, 20000, 65536])
+def test_cell_counts_from_two_to_the_maximum(pkg, n_cells):
+    """Odd, tiny and very long patterns at the headline order; beyond ~10^4 cells the register-tile front kernel no longer
+    holds the pattern tables in shared memory and the handle plans the generic kernels instead."""
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(n_cells)
+    pats = np.stack([rng.choice([-1, 1], n_cells), np.repeat(rng.choice([-1, 1], -(-n_cells // 5)), 5)[:n_cells]]).astype(np.int8)
+    be = pkg.RCWABatch(n_cells, 40, max_batch=4)
+    eff, r3, t3, st = be.evaluate_host(pats, 1100.0, 60.0, 325.0, return_orders=True)
+    assert not st.any()
+    for i in range(2):
+        r = O.evaluate(pats[i].astype(np.float64), 1100.0, 60.0, 40, 325.0)
+        assert abs(eff[i] - r.eff) <= TIGHT, (n_cells, i, eff[i], r.eff)
+    be.close()
+
+
+def test_extreme_thickness_wavelength_angle(pkg):
+    from oracle import rcwa_oracle as O
+    pats = np.repeat(np.random.default_rng(5).choice([-1, 1], (1, 32)), 8, axis=1).astype(np.int8)
+    be = pkg.RCWABatch(256, 40, max_batch=4)
+    for thick in (1.0, 100.0, 5000.0, 50000.0):
+        for wl, ang in ((1100.0, 60.0), (400.0, 20.0), (2000.0, 85.0), (1100.0, 5.0)):
+            eff, st = be.evaluate_host(pats, wl, ang, thick), None
+            ref = O.evaluate(pats[0].astype(np.float64), wl, ang, 40, thick).eff
+            assert abs(eff[0] - ref) <= TIGHT, (thick, wl, ang, eff[0], ref)
+    be.close()
+
+
 def test_other_wavelengths_angles_thickness_vs_oracle(pkg):
     from oracle import rcwa_oracle as O
     rng = np.random.default_rng(77)
