@@ -118,6 +118,23 @@ def test_batch_4096_properties(pkg, torch_mod):
     be.close(); be2.close()
 
 
+@pytest.mark.parametrize("order,B", [(40, 2501), (60, 1301)])
+def test_gradient_pipeline_equals_serial_launches(pkg, torch_mod, order, B):
+    """Odd batch through the sub-chunk pipeline (two unequal halves) against the same call with the pipeline off."""
+    torch = torch_mod
+    pats = torch.from_numpy((np.random.default_rng(B).integers(0, 2, (B, 256)) * 2 - 1).astype(np.int8)).cuda()
+    be = pkg.RCWABatch(256, order, max_batch=4096, device=0)
+    eff, grad, st = be.evaluate_grad(pats)
+    be.set_subchunk(0)
+    eff0, grad0, st0 = be.evaluate_grad(pats)
+    torch.cuda.synchronize()
+    assert int(st.abs().sum()) == 0 and int(st0.abs().sum()) == 0
+    assert torch.equal(eff, eff0)
+    scale = grad0.abs().amax(dim=1, keepdim=True)
+    assert bool(((grad - grad0).abs() <= 1e-13 + 1e-11 * scale).all())     # shared-memory atomics: summation order differs
+    be.close()
+
+
 def test_gradient_is_not_the_flip_delta_but_bounds_small_steps(pkg, torch_mod):
     """Directional check entirely on the device: for a pattern with two cells blended half way (not representable as int8)
     we cannot call the forward path, so instead check the symmetric identity sum_p grad_p * 0 = 0 trivially and the
