@@ -943,44 +943,52 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
 // 16 x 16 threads, 6 x 6 register tile per thread (rows ty + 16 r, columns tx + 16 c) over 96 x 96 blocks of C.
 // C must not alias A or B.
 // ===================================================================================================
-template <bool TRANS_B>
-__device__ __forceinline__ void cta_gemm(double* __restrict__ C, const double* __restrict__ A, const double* __restrict__ B,
-                                         int ff, int ld) {
+template <bool TRANS_B, int RT>
+__device__ __forceinline__ void cta_gemm_rt(double* __restrict__ C, const double* __restrict__ A, const double* __restrict__ B,
+                                            int ff, int ld) {
+  constexpr int BLK = 16 * RT;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  for (int i0 = 0; i0 < ff; i0 += 96)
-    for (int j0 = 0; j0 < ff; j0 += 96) {
-      double acc[6][6];
-      int ri[6], cj[6];
+  for (int i0 = 0; i0 < ff; i0 += BLK)
+    for (int j0 = 0; j0 < ff; j0 += BLK) {
+      double acc[RT][RT];
+      int ri[RT], cj[RT];
 #pragma unroll
-      for (int r = 0; r < 6; ++r) {
+      for (int r = 0; r < RT; ++r) {
         ri[r] = min(i0 + ty + 16 * r, ff - 1) * ld;
         cj[r] = min(j0 + tx + 16 * r, ff - 1);
         if (TRANS_B) cj[r] *= ld;
 #pragma unroll
-        for (int c = 0; c < 6; ++c) acc[r][c] = 0.0;
+        for (int c = 0; c < RT; ++c) acc[r][c] = 0.0;
       }
       for (int k = 0; k < ff; ++k) {
-        double a[6], bq[6];
+        double a[RT], bq[RT];
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
+        for (int r = 0; r < RT; ++r) {
           a[r] = A[ri[r] + k];
           bq[r] = TRANS_B ? B[cj[r] + k] : B[k * ld + cj[r]];
         }
 #pragma unroll
-        for (int r = 0; r < 6; ++r)
+        for (int r = 0; r < RT; ++r)
 #pragma unroll
-          for (int c = 0; c < 6; ++c) acc[r][c] = fma(a[r], bq[c], acc[r][c]);
+          for (int c = 0; c < RT; ++c) acc[r][c] = fma(a[r], bq[c], acc[r][c]);
       }
 #pragma unroll
-      for (int r = 0; r < 6; ++r) {
+      for (int r = 0; r < RT; ++r) {
         const int i = i0 + ty + 16 * r;
 #pragma unroll
-        for (int c = 0; c < 6; ++c) {
+        for (int c = 0; c < RT; ++c) {
           const int j = j0 + tx + 16 * c;
           if (i < ff && j < ff) C[i * ld + j] = acc[r][c];
         }
       }
     }
+}
+// register tile 6 x 6 (96 x 96 per pass) up to ff = 96, 8 x 8 (128 x 128 per pass) beyond: ff = 121 is one pass instead of four
+template <bool TRANS_B>
+__device__ __forceinline__ void cta_gemm(double* __restrict__ C, const double* __restrict__ A, const double* __restrict__ B,
+                                         int ff, int ld) {
+  if (ff <= 96) cta_gemm_rt<TRANS_B, 6>(C, A, B, ff, ld);
+  else cta_gemm_rt<TRANS_B, 8>(C, A, B, ff, ld);
 }
 
 // q = sqrt(lambda) (principal branch), X = exp(-k0 d q)
@@ -1105,8 +1113,9 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
       for (int r = 0; r < PIRL_GRAD_NV / 2; ++r) vi[r] = make_double2(Vf[i * vsm + 2 * r * vsr], Vf[i * vsm + (2 * r + 1) * vsr]);
       const double lmi = lam[i];
       const cplx qi = qS[i], Xi = XS[i];
-      for (int j = lane; j < ff; j += 32) {
-        M0[i * ld + j] = Wg[i * ff + j];
+      for (int j = lane; j < ff; j += 32) M0[i * ld + j] = Wg[i * ff + j];
+      // G_B and G_A are symmetric (K_ij = K_ji): the diagonal and the pairs j > i are computed, the mirror image is stored too
+      for (int j = i + lane; j < ff; j += 32) {
         double pij = 0.0, pji = 0.0;
 #pragma unroll
         for (int r = 0; r < PIRL_GRAD_RANK; ++r) {
@@ -1154,8 +1163,9 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
         acc = cfma(cconj(SD), dD1, acc);
         acc = cfma(cconj(SXQ), dXQ, acc);
         const double K = acc.x;
-        M1[i * ld + j] = 0.5 * K;
-        M2[i * ld + j] = -0.5 * fma(0.5 * (lmi + lmj), K, 0.5 * (pij + pji));
+        const double gb = 0.5 * K, ga = -0.5 * fma(0.5 * (lmi + lmj), K, 0.5 * (pij + pji));
+        M1[i * ld + j] = gb; M1[j * ld + i] = gb;
+        M2[i * ld + j] = ga; M2[j * ld + i] = ga;
       }
     }
     __syncthreads();
