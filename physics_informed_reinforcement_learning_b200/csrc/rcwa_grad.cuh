@@ -28,6 +28,7 @@ struct GParams {
   double* gscratch;    // per-CTA scratch (L2 resident)
   size_t gstride;      // doubles per CTA
   int smem_mats;       // matrices held in shared memory (kernel specific)
+  int packed;          // g_tail, shared-memory variant: G_II is inverted as a packed lower triangle in shared memory
 };
 
 __host__ __device__ inline int grad_tail_vec_doubles(int ff) { return tail_vec_doubles(ff) + pirl_even(ff / 2 + 2) + pirl_even(ff); }
@@ -481,6 +482,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
   cplx* Sm = (REG || G.smem_mats >= 2) ? reinterpret_cast<cplx*>(mat0) + csz : spill + csz;
   double* Wr = reinterpret_cast<double*>(Sm);
   cplx* gv = spill + 2 * csz;                       // 16 global vectors
+  cplx* Pk = reinterpret_cast<cplx*>(mat0);         // packed lower triangle of G_II (G.packed)
   cplx* v_ell = gv;           cplx* v_x = gv + ff;       cplx* v_yb = gv + 2 * ff;  cplx* v_qb = gv + 3 * ff;
   cplx* v_Xb = gv + 4 * ff;   cplx* v_hb = gv + 5 * ff;  cplx* v_w2 = gv + 6 * ff;  cplx* v_pw2 = gv + 7 * ff;
   cplx* v_x2 = gv + 8 * ff;   cplx* v_pm = gv + 9 * ff;  cplx* v_in = gv + 10 * ff; /* 6 vectors: v_in .. v_in + 6 ff */
@@ -670,13 +672,47 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
           cplx g = aII[c], h = aI[c];
           HII[(size_t)i * ff + j] = g;
           if (i == j) { g = cadd(g, qv[i]); h = csub(h, qv[i]); }
-          Pm[i * ld + j] = g;
+          if (!G.packed) Pm[i * ld + j] = g;
+          else if (j <= i) Pk[i * (i + 1) / 2 + j] = g;
           Hq[(size_t)i * ff + j] = h;
         }
       }
     }
-    // ---- P = G_II^-1 : complex symmetric Gauss-Jordan, no pivoting ----
+    // ---- P = G_II^-1 : complex symmetric, no pivoting ----
     RK_PHASE(16);
+    if (G.packed) {
+      // Neither complex matrix fits in shared memory at this size, but the lower triangle of the symmetric G_II does:
+      // symmetric sweep operator (A_kk <- -1/A_kk, A_ik <- A_ik / A_kk, A_ij <- A_ij - A_ik A_kj / A_kk keeps A symmetric and
+      // ends at -A^-1), one staged column per step instead of a pass over the whole matrix through L2
+      const int npair = (ff + 1) >> 1;
+      for (int k = 0; k < ff; ++k) {
+        __syncthreads();
+        for (int t = tid; t < ff; t += NT) colk[t] = (t >= k) ? Pk[t * (t + 1) / 2 + k] : Pk[k * (k + 1) / 2 + t];
+        __syncthreads();
+        const cplx p = cinv(colk[k]);
+        for (int pr = warp; pr < npair; pr += NW) {      // rows in pairs (r, ff - 1 - r): equal work per warp
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            const int i = half ? ff - 1 - pr : pr;
+            if (half && i == pr) continue;
+            cplx* row = Pk + i * (i + 1) / 2;
+            if (i == k) {
+              for (int j = lane; j <= i; j += 32) row[j] = (j == k) ? make_double2(-p.x, -p.y) : cmul(colk[j], p);
+            } else {
+              const cplx f = cmul(colk[i], p);
+              for (int j = lane; j <= i; j += 32) row[j] = (j == k) ? f : cfnma(f, colk[j], row[j]);
+            }
+          }
+        }
+      }
+      __syncthreads();
+      for (int i = warp; i < ff; i += NW)
+        for (int j = lane; j < ff; j += 32) {
+          const int a = max(i, j), b2 = min(i, j);
+          const cplx v = Pk[a * (a + 1) / 2 + b2];
+          Pm[i * ld + j] = make_double2(-v.x, -v.y);
+        }
+    } else
     for (int k = 0; k < ff; ++k) {
       __syncthreads();
       for (int t = tid; t < ff; t += NT) { rowk[t] = Pm[k * ld + t]; colk[t] = Pm[t * ld + k]; }
