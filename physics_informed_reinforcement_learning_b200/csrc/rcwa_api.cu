@@ -73,7 +73,7 @@ struct pirl_handle {
   cudaStream_t own_stream = nullptr;
   // adjoint gradient (allocated on the first pirl_rcwa_eval_grad)
   double *g_lamb = nullptr, *g_Lf = nullptr, *g_Rf = nullptr, *g_Vf = nullptr, *g_Einv = nullptr, *g_scr_tail = nullptr, *g_scr_eig = nullptr;
-  int g_tail_grid = 0, g_tail_mats = 0, g_eig_grid = 0, g_eig_mats = 0; bool g_tail_regtile = false; int g_tail_packed = 0;
+  int g_tail_grid = 0, g_tail_mats = 0, g_eig_grid = 0, g_eig_mats = 0; bool g_tail_regtile = false; int g_tail_packed = 0, g_tail_lu_k0 = 0;
   size_t g_tail_smem = 0, g_eig_smem = 0, g_tail_stride = 0, g_eig_stride = 0;
   double* hd_grad = nullptr; int64_t hd_grad_cap = 0;
   // per-kernel timing (pirl_rcwa_set_stage_timing)
@@ -484,7 +484,7 @@ static GParams sub_gparams(const GParams& G0, int n_cells, int ff, int off) {
 
 static void launch_gtail(pirl_handle* h, const KParams& P, GParams G, cudaStream_t st) {
   StageTimer t(h, 7, st);
-  G.gscratch = h->g_scr_tail; G.gstride = h->g_tail_stride; G.smem_mats = h->g_tail_mats; G.packed = h->g_tail_packed;
+  G.gscratch = h->g_scr_tail; G.gstride = h->g_tail_stride; G.smem_mats = h->g_tail_mats; G.packed = h->g_tail_packed; G.lu_k0 = h->g_tail_lu_k0;
   const int g = std::min(P.B, h->g_tail_grid);
   if (h->g_tail_regtile) g_tail<GTAIL_NT, 3><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
   else if (h->ff <= 128) g_tail<GTAIL_NT, 4><<<g, GTAIL_NT, h->g_tail_smem, st>>>(P, G);
@@ -494,7 +494,7 @@ static void launch_gtail(pirl_handle* h, const KParams& P, GParams G, cudaStream
 
 static void launch_geig(pirl_handle* h, const KParams& P, GParams G, cudaStream_t st) {
   StageTimer t(h, 8, st);
-  G.gscratch = h->g_scr_eig; G.gstride = h->g_eig_stride; G.smem_mats = h->g_eig_mats; G.packed = 0;
+  G.gscratch = h->g_scr_eig; G.gstride = h->g_eig_stride; G.smem_mats = h->g_eig_mats; G.packed = 0; G.lu_k0 = 0;
   if (h->g_eig_mats >= 4) g_eigback<GEIG_NT, true><<<std::min(P.B, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
   else g_eigback<GEIG_NT, false><<<std::min(P.B, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
   h->launches += 1;
@@ -749,7 +749,15 @@ static int grad_prepare(pirl_handle* h) {
   if (rc) return rc;
   {   // no matrix in shared memory (ff >= 115): the packed lower triangle of G_II may still fit
     const size_t pk = (size_t)ff * (ff + 1) / 2 * sizeof(cplx);
-    if (!h->g_tail_regtile && h->g_tail_mats == 0 && tvec + pk <= h->smem_optin - 1024) { h->g_tail_packed = 1; h->g_tail_smem = tvec + pk; }
+    if (!h->g_tail_regtile && h->g_tail_mats == 0 && tvec + pk <= h->smem_optin - 1024) {
+      // ... and so does the trailing block of S after the first lu_k0 elimination steps (same storage, later)
+      const size_t avail = h->smem_optin - 1024 - tvec;
+      int side = ff;
+      while (side > 0 && (size_t)side * side * sizeof(cplx) > avail) --side;
+      h->g_tail_packed = 1;
+      h->g_tail_lu_k0 = ff - side;
+      h->g_tail_smem = tvec + std::max(pk, (size_t)side * side * sizeof(cplx));
+    }
   }
   const size_t evec = (size_t)grad_eig_vec_doubles(ff, h->cfg.n_cells) * 8;
   if (mats_that_fit(h->smem_optin - 1024, evec, rmat, 4) == 4)   // all four in shared memory: variant with shared pointers only

@@ -29,6 +29,7 @@ struct GParams {
   size_t gstride;      // doubles per CTA
   int smem_mats;       // matrices held in shared memory (kernel specific)
   int packed;          // g_tail, shared-memory variant: G_II is inverted as a packed lower triangle in shared memory
+  int lu_k0;           // ... and the trailing block [lu_k0, ff)^2 of S is factorised in shared memory (ff: never)
 };
 
 __host__ __device__ inline int grad_tail_vec_doubles(int ff) { return tail_vec_doubles(ff) + pirl_even(ff / 2 + 2) + pirl_even(ff); }
@@ -759,12 +760,26 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
     RK_PHASE(18);
     for (int t = tid; t < ff; t += NT) bvec[t] = cscale(r0, wr[2 * ff + t]);
     // ---- P_r S = L U with partial pivoting; multipliers kept below the diagonal, pivots in ipiv ----
+    // S does not fit in shared memory at the sizes of this variant, but its trailing block does after a few steps: from step
+    // k0s on the block [k0s, ff)^2 is factorised in shared memory (the storage of the packed G_II, free by now) and written back
+    // at the end; the L columns left of it stay in L2 and only take part in the row swaps.
+    const int k0s = G.packed ? G.lu_k0 : ff;
+    const int ldt = ff - k0s;
+    cplx* Ts = reinterpret_cast<cplx*>(mat0);
+    bool staged = false;
+#define PIRL_SEL(i, j) (*((staged && (j) >= k0s) ? &Ts[((i) - k0s) * ldt + ((j) - k0s)] : &Sm[(i) * ld + (j)]))
     for (int k = 0; k < ff; ++k) {
       __syncthreads();
+      if (k == k0s) {
+        for (int i = k0s + warp; i < ff; i += NW)
+          for (int j = k0s + lane; j < ff; j += 32) Ts[(i - k0s) * ldt + (j - k0s)] = Sm[i * ld + j];
+        staged = true;
+        __syncthreads();
+      }
       if (warp == 0) {
         double best = -1.0; int bi = k;
         for (int i = k + lane; i < ff; i += 32) {
-          cplx a = Sm[i * ld + k];
+          cplx a = PIRL_SEL(i, k);
           double mg = fabs(a.x) + fabs(a.y);
           if (mg > best) { best = mg; bi = i; }
         }
@@ -779,17 +794,23 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
       __syncthreads();
       const int pv = ipiv[k];
       if (pv != k) {
-        for (int j = tid; j < ff; j += NT) { cplx t = Sm[k * ld + j]; Sm[k * ld + j] = Sm[pv * ld + j]; Sm[pv * ld + j] = t; }
+        for (int j = tid; j < ff; j += NT) { cplx t = PIRL_SEL(k, j); PIRL_SEL(k, j) = PIRL_SEL(pv, j); PIRL_SEL(pv, j) = t; }
         if (tid == 0) { cplx t = bvec[k]; bvec[k] = bvec[pv]; bvec[pv] = t; }
         __syncthreads();
       }
-      const cplx pinv = cinv(Sm[k * ld + k]);
+      const cplx pinv = cinv(PIRL_SEL(k, k));
       const cplx bk = bvec[k];
       for (int i = k + 1 + warp; i < ff; i += NW) {
-        const cplx f = cmul(Sm[i * ld + k], pinv);
-        for (int j = k + 1 + lane; j < ff; j += 32) Sm[i * ld + j] = cfnma(f, Sm[k * ld + j], Sm[i * ld + j]);
-        if (lane == 0) { bvec[i] = cfnma(f, bk, bvec[i]); Sm[i * ld + k] = f; }
+        const cplx f = cmul(PIRL_SEL(i, k), pinv);
+        for (int j = k + 1 + lane; j < ff; j += 32) PIRL_SEL(i, j) = cfnma(f, PIRL_SEL(k, j), PIRL_SEL(i, j));
+        if (lane == 0) { bvec[i] = cfnma(f, bk, bvec[i]); PIRL_SEL(i, k) = f; }
       }
+    }
+#undef PIRL_SEL
+    if (staged) {
+      __syncthreads();
+      for (int i = k0s + warp; i < ff; i += NW)
+        for (int j = k0s + lane; j < ff; j += 32) Sm[i * ld + j] = Ts[(i - k0s) * ldt + (j - k0s)];
     }
     }
     __syncthreads();
