@@ -481,7 +481,9 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
   // that may be shared or global compiles to generic loads with 64-bit address arithmetic in the inner loops)
   cplx* Pm = (REG || G.smem_mats >= 1) ? reinterpret_cast<cplx*>(mat0) : spill;
   cplx* Sm = (REG || G.smem_mats >= 2) ? reinterpret_cast<cplx*>(mat0) + csz : spill + csz;
-  double* Wr = reinterpret_cast<double*>(Sm);
+  // W staged in S's storage; in the packed mode of the shared-memory variant S lives in L2, W then takes the (still empty)
+  // shared storage of the packed G_II
+  double* Wr = (!REG && G.packed) ? mat0 : reinterpret_cast<double*>(Sm);
   cplx* gv = spill + 2 * csz;                       // 16 global vectors
   cplx* Pk = reinterpret_cast<cplx*>(mat0);         // packed lower triangle of G_II (G.packed)
   cplx* v_ell = gv;           cplx* v_x = gv + ff;       cplx* v_yb = gv + 2 * ff;  cplx* v_qb = gv + 3 * ff;
@@ -673,11 +675,15 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
           cplx g = aII[c], h = aI[c];
           HII[(size_t)i * ff + j] = g;
           if (i == j) { g = cadd(g, qv[i]); h = csub(h, qv[i]); }
-          if (!G.packed) Pm[i * ld + j] = g;
-          else if (j <= i) Pk[i * (i + 1) / 2 + j] = g;
+          Pm[i * ld + j] = g;
           Hq[(size_t)i * ff + j] = h;
         }
       }
+    }
+    if (G.packed) {   // W is dead: its storage takes the lower triangle of G_II
+      __syncthreads();
+      for (int i = warp; i < ff; i += NW)
+        for (int j = lane; j <= i; j += 32) Pk[i * (i + 1) / 2 + j] = Pm[i * ld + j];
     }
     // ---- P = G_II^-1 : complex symmetric, no pivoting ----
     RK_PHASE(16);
@@ -742,7 +748,7 @@ __global__ void __launch_bounds__(NT) g_tail(KParams P, GParams G) {
 #pragma unroll
         for (int c = 0; c < NCOL; ++c) {
           const int j = lane + 32 * c;
-          if (j < ff) acc[c] = cfma(f, Pm[k * ld + j], acc[c]);
+          if (j < ff) acc[c] = cfma(f, Pm[k * ld + j], acc[c]);   // (reading the packed P from shared memory instead: slower, gather)
         }
       }
 #pragma unroll
