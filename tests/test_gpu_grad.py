@@ -77,6 +77,20 @@ def test_every_kernel_variant_against_oracle_fd(pkg, order):
     be.close()
 
 
+@pytest.mark.parametrize("n_cells,order", [(20000, 40), (12000, 60)])
+def test_gradient_on_very_long_patterns(pkg, n_cells, order):
+    """Pattern tables too long for the register-tile front kernel: the generic kernels export E^-1 for the adjoint sweep."""
+    from oracle import rcwa_oracle
+    pat = np.repeat(np.random.default_rng(n_cells).choice([-1.0, 1.0], -(-n_cells // 50)), 50)[:n_cells]
+    be = pkg.RCWABatch(n_cells, order, max_batch=2, device=0)
+    eff, grad, st = be.evaluate_grad_host(pat[None, :])
+    idx = [0, n_cells // 3, n_cells - 1]
+    fd = rcwa_oracle.fd_gradient(pat, idx, order=order)
+    assert st[0] == 0
+    assert _close(grad[0, idx], fd).all(), (grad[0, idx], fd)
+    be.close()
+
+
 def test_uniform_and_degenerate_patterns(pkg, torch_mod):
     """Uniform slabs have exactly degenerate cos/sin mode pairs: the degenerate pairs must drop out, not produce inf/nan."""
     from oracle import rcwa_oracle
