@@ -1,4 +1,9 @@
-"""Build the C-ABI CUDA library in-tree with nvcc for sm_100a (no JIT cache: the .so travels with the repo)."""
+"""Build the C-ABI CUDA library in-tree with nvcc for sm_100a (no JIT cache: the .so travels with the repo).
+
+Two translation units (compiled to objects under csrc/build/, linked into libpirl_rcwa.so):
+  rcwa_api.cu      C ABI + the single-SM kernels (rcwa_kernels / rcwa_regtile / rcwa_tail2 / rcwa_grad)
+  rcwa_cluster.cu  thread-block-cluster kernels for the large orders (rcwa_cluster.cuh)
+"""
 from __future__ import annotations
 
 import os
@@ -7,14 +12,21 @@ import subprocess
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
+OBJ_DIR = os.path.join(CSRC, "build")
 LIB_PATH = os.path.join(PKG_DIR, "libpirl_rcwa.so")
-SOURCES = ["rcwa_api.cu"]
-DEPENDS = ["rcwa_api.cu", "rcwa_kernels.cuh", "rcwa_regtile.cuh", "rcwa_tail2.cuh", "rcwa_grad.cuh", os.path.join("..", "..", "include", "pirl_rcwa.h")]
+HEADER = os.path.join("..", "..", "include", "pirl_rcwa.h")
+# source -> files whose change makes its object stale
+UNITS = {
+    "rcwa_api.cu": ["rcwa_api.cu", "rcwa_common.cuh", "rcwa_kernels.cuh", "rcwa_regtile.cuh", "rcwa_tail2.cuh",
+                    "rcwa_grad.cuh", "rcwa_cluster.h", HEADER],
+    "rcwa_cluster.cu": ["rcwa_cluster.cu", "rcwa_cluster.cuh", "rcwa_cluster_tail.cuh", "rcwa_cluster.h", "rcwa_common.cuh"],
+}
+SOURCES = list(UNITS)
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC",
 ]
 
 
@@ -25,24 +37,55 @@ def find_nvcc() -> str:
     raise RuntimeError("nvcc not found: the CUDA library cannot be built (there is no CPU fallback)")
 
 
+def _obj(src: str) -> str:
+    return os.path.join(OBJ_DIR, os.path.splitext(src)[0] + ".o")
+
+
+def _mtime(rel: str) -> float:
+    p = os.path.join(CSRC, rel)
+    return os.path.getmtime(p) if os.path.exists(p) else 0.0
+
+
+def _unit_stale(src: str) -> bool:
+    o = _obj(src)
+    if not os.path.exists(o):
+        return True
+    t = os.path.getmtime(o)
+    return any(_mtime(d) > t for d in UNITS[src])
+
+
 def is_stale() -> bool:
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
-    return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPENDS)
+    return any(_mtime(d) > t for deps in UNITS.values() for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
-        return LIB_PATH
-    cmd = [find_nvcc()] + NVCC_FLAGS + [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB_PATH]
-    if verbose:
-        cmd.insert(1, "-Xptxas=-v")
+def _run(cmd, verbose):
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    if not force and not is_stale():
+        return LIB_PATH
+    nvcc = find_nvcc()
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    procs = []
+    for src in SOURCES:
+        if force or _unit_stale(src):
+            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas=-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", _obj(src)]
+            procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)))
+    for src, p in procs:       # the units compile in parallel
+        out, err = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError(f"nvcc failed on {src}:\n" + out + err)
+        if verbose:
+            print(err)
+    _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC"] + [_obj(s) for s in SOURCES] + ["-o", LIB_PATH], verbose)
     return LIB_PATH
 
 

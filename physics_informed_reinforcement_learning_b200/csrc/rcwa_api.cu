@@ -5,6 +5,7 @@
 #include "rcwa_regtile.cuh"
 #include "rcwa_tail2.cuh"
 #include "rcwa_grad.cuh"
+#include "rcwa_cluster.h"
 #include "../../include/pirl_rcwa.h"
 
 #include <complex>
@@ -64,6 +65,8 @@ struct pirl_handle {
   unsigned long long* trace = nullptr;       // CTA trace records (PIRL_TRACE=1)
   bool no_rktail = false, old_rktail = false; int rk_tail2_grid = 0; size_t rk_tail2_smem = 0;
   bool regfront121 = false;   // ff = 121: padded register-tile front kernel, shared-memory kernels behind it
+  // thread-block-cluster path (rcwa_cluster.cu): orders whose matrices do not fit one SM
+  bool cluster = false; ClusterPlan cplan; double* cscratch = nullptr;
   bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
@@ -83,8 +86,8 @@ struct pirl_handle {
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
 };
 
-static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail", "g_tail", "g_eigback"};
-static constexpr int kNumStages = 9;
+static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail", "g_tail", "g_eigback", "ck_front", "ck_tail"};
+static constexpr int kNumStages = 11;
 
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
 #ifdef PIRL_FRONT_9x9
@@ -303,6 +306,18 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     if (per_sm < 1) return fail(-9, "rk_tail2 (order 60) does not fit on this device");
     h->rk_tail2_grid = h->sm_count * per_sm;
   }
+  // cluster path: every order without a single-SM register-tile kernel whose padded matrix fits the 208 x 208 cluster tile
+  // (PIRL_FORCE_CLUSTER=1: the 84 x 84 test variant for orders <= 41; PIRL_NO_CLUSTER=1: generic kernels)
+  if (!h->regtile && !h->regfront121 && !getenv("PIRL_NO_CLUSTER")) {
+    const bool small = getenv("PIRL_FORCE_CLUSTER") != nullptr && ff <= 84;
+    if (small || (ff > 81 && ff <= kClusterFF)) {
+      CUDA_TRY(ck_plan(ff, nc, h->smem_optin, small, &h->cplan));
+      if (h->cplan.front_ok) {
+        h->cluster = true;
+        CUDA_TRY(dmalloc(&h->cscratch, (size_t)h->cplan.front_clusters * h->cplan.front_scratch_doubles));
+      }
+    }
+  }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
   CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<96, 4, 96>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
@@ -349,7 +364,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaFree(h->d_tw); cudaFree(h->d_Dk);
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
   cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace); cudaFree(h->queues);
-  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status);
+  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status); cudaFree(h->cscratch);
   cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_Vf); cudaFree(h->g_Einv); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
@@ -389,7 +404,13 @@ static int* next_queue(pirl_handle* h, cudaStream_t st) {
 }
 
 static void launch_front(pirl_handle* h, KParams P, cudaStream_t st) {
-  if (h->regfront121) {
+  if (h->cluster) {
+    if (P.B > h->cplan.front_clusters) P.queue = next_queue(h, st);
+    StageTimer t(h, 9, st);
+    cudaError_t e = ck_launch_front(h->cplan, P, h->cscratch, st);
+    if (e != cudaSuccess && h->sync_fail_stage < 0) { h->sync_fail_stage = 9; h->sync_err = e; }
+    h->launches += 1;
+  } else if (h->regfront121) {
     if (P.B > h->rk_front_grid) P.queue = next_queue(h, st);
     StageTimer t(h, 5, st);
     rk_front<Cfg121><<<std::min(P.B, h->rk_front_grid), Cfg121::NT, h->rk_front_smem, st>>>(P);
@@ -426,7 +447,15 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
 }
 
 static void launch_tail(pirl_handle* h, KParams P, cudaStream_t st) {
-  if (h->regfront121 && !h->no_rktail) {
+  if (h->cluster && h->cplan.tail_ok && !h->no_rktail) {
+    if (P.B > h->cplan.tail_clusters) P.queue = next_queue(h, st);
+    StageTimer t(h, 10, st);
+    cudaError_t e = ck_launch_tail(h->cplan, P, st);
+    if (e != cudaSuccess && h->sync_fail_stage < 0) { h->sync_fail_stage = 10; h->sync_err = e; }
+    P.fallback_only = 1;
+    P.queue = nullptr;
+    h->launches += 1;
+  } else if (h->regfront121 && !h->no_rktail) {
     if (P.B > h->rk_tail2_grid) P.queue = next_queue(h, st);
     StageTimer t(h, 6, st);
     RK_TAIL2_121<<<std::min(P.B, h->rk_tail2_grid), Cfg121::NT, h->rk_tail2_smem, st>>>(P);
