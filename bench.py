@@ -35,6 +35,15 @@ UNIT = "evals/s"
 WORKLOAD = "configs[1]: 4096 random 256-pixel patterns per GPU, 1100 nm / 60 deg, TM, order 40, float64 (complex128-equivalent)"
 
 
+def workload_name(args) -> str:
+    """configs[1] (the default, the configuration BASELINE.json's metric is quoted on) or the named other configuration."""
+    if (args.n_cells, args.order, args.batch) == (256, 40, 4096):
+        return WORKLOAD
+    tag = "configs[4] (C5)" if (args.n_cells, args.order) == (512, 100) else "configs[3] (C4) size" if args.order == 60 else "custom"
+    return (f"{tag}: {args.batch} random {args.n_cells}-pixel patterns per GPU, {args.wavelength:g} nm / {args.angle:g} deg, TM, "
+            f"order {args.order}, float64 (complex128-equivalent)")
+
+
 def f_alg(ff: int) -> float:
     """Algorithmic real FP64 flops per evaluation: (220/3) ff^3."""
     return 220.0 / 3.0 * ff ** 3
@@ -49,7 +58,8 @@ STAGE_FLOPS_FF3 = {
     "k_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
     "rk_front": 28.0 / 3.0 + 44.0 / 3.0,       # register-tile fusion of k_front + k_tridiag
     "rk_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
-    "k_solve": 220.0 / 3.0,                    # fused whole-path kernel
+    "ck_front": 28.0 / 3.0 + 44.0 / 3.0,       # thread-block-cluster kernels of the large orders: same stages
+    "ck_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
 }
 
 
@@ -174,7 +184,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "n_cells": args.n_cells, "order": args.order, "batch_per_step": per_step},
+            "config": {"workload": workload_name(args), "n_cells": args.n_cells, "order": args.order, "batch_per_step": per_step,
+                       "note": f"rate metric: each step times {per_step} of the {args.batch} patterns of the workload"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -230,7 +241,8 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    be = RCWABatch(args.n_cells, args.order, max_batch=args.batch, device=local_rank)
+    max_batch = args.max_batch or (args.batch if args.order <= 60 else min(args.batch, 4096))   # workspace chunk (ff = 201: 3.3 MB per structure)
+    be = RCWABatch(args.n_cells, args.order, max_batch=max_batch, device=local_rank)
     d_pats = torch.from_numpy(pats_np).to(dev)
     params_rows, _ = be._params(1, args.wavelength, args.angle, args.thickness, None)
     d_params = torch.from_numpy(params_rows).to(dev)
@@ -245,9 +257,21 @@ def run_b200(args):
     fp64_peak = measure_fp64_peak(torch) if rank == 0 else None
 
     # ---- device-resident arm -------------------------------------------------------------------------------------
+    # N > 1: every step ends with the design's ONE data-path collective: an NCCL all_gather of the
+    # float64 efficiencies of all ranks (8 B per structure), inside the event-timed region.
+    from physics_informed_reinforcement_learning_b200 import gather_efficiencies, shard_range
+    gathered = torch.empty(args.batch * world, dtype=torch.float64, device=dev) if world > 1 else None
+
+    def step(pats, out=None, total=None):
+        e = be.evaluate(pats, params=d_params)
+        if world > 1:
+            gather_efficiencies(e, total if total is not None else args.batch * world, out=out)
+        return e
+
     eff = None
-    for _ in range(max(args.warmup, 3)):
-        eff = be.evaluate(d_pats, params=d_params)
+    n_warm = max(args.warmup, 3)
+    for _ in range(n_warm):
+        eff = step(d_pats, gathered)
     torch.cuda.synchronize()
     eff_first = eff.clone()
 
@@ -258,11 +282,21 @@ def run_b200(args):
     sampler.start()
     for a, b in ev:
         flush.fill_(1)                       # evict L2 between timed iterations (untimed)
+        if not args.no_sync_after_flush:
+            # the flush kernel's dirty lines drain while the next kernels start: without this sync the timed step inherits
+            # 0.15-0.25 ms of the flush's HBM write-back and reads SLOWER than the end-to-end arm, which syncs before its
+            # wall-clock timer (profiles/r02c_bench*.json: 504.9k vs 520.5k evals/s, e2e 512.7k / 517.8k)
+            torch.cuda.synchronize()
         a.record()
-        eff = be.evaluate(d_pats, params=d_params)
+        eff = step(d_pats, gathered)
         b.record()
     barrier()
     launches = be.launch_count() - l0
+    if world > 1:
+        assert torch.equal(gathered[rank * args.batch:(rank + 1) * args.batch], eff), "all_gather: own shard differs"
+        chk = gathered.view(world, args.batch).sum(dim=1)          # every rank holds every shard: compare the shard sums
+        chk0 = chk.clone(); dist.broadcast(chk0, 0)
+        assert torch.equal(chk, chk0), "all_gather: ranks hold different vectors"
     # per-kernel durations for the roofline: the same steps once more with the internal sub-chunk pipeline off, so that every
     # kernel runs alone between its two events (in the pipelined timed region kernels of the two half-chunks overlap and a
     # per-kernel duration is not defined); this is also how the ncu launch list in profiles/ sees them (serialised)
@@ -322,6 +356,53 @@ def run_b200(args):
         grad_info = {"value": args.batch / (gms * 1e-3), "unit": "gradients/s per GPU (efficiency + d eff / d 256 cells)",
                      "ms_per_step": gms, "gpu_launches": int(be.launch_count() - gl0), "steps": gsteps}
 
+    # ---- strong-scaling leg: FIXED global batch cut in contiguous shard_range blocks, all_gather inside the timed step ----
+    strong = None
+    if world > 1 and not args.no_strong:
+        G = args.strong_batch or args.batch
+        lo, hi = shard_range(G, rank, world)
+        g_pats = torch.from_numpy(make_patterns(G, args.n_cells, 99)[lo:hi].copy()).to(dev)
+        g_out = torch.empty(G, dtype=torch.float64, device=dev)
+        for _ in range(n_warm):
+            step(g_pats, g_out, G)
+        sev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        barrier()
+        for a, b in sev:
+            flush.fill_(1)
+            a.record()
+            step(g_pats, g_out, G)
+            b.record()
+        barrier()
+        s_job = max_over_ranks(sum(a.elapsed_time(b) for a, b in sev) * 1e-3, device=dev)
+        strong = {"global_batch": G, "structures_per_gpu": hi - lo, "value": G * args.steps / s_job, "unit": UNIT,
+                  "ms_per_step": s_job / args.steps * 1e3,
+                  "note": "fixed total batch in contiguous shards, NCCL all_gather of the efficiencies inside the timed step"}
+    elif world == 1:
+        strong = {"global_batch": args.batch, "structures_per_gpu": args.batch, "value": args.batch * args.steps / job_s,
+                  "unit": UNIT, "ms_per_step": job_s / args.steps * 1e3, "note": "N = 1: same run as `value`"}
+
+    # ---- single-call latency (BASELINE configs[0]): one MeentIndex.get_efficiency call, host buffers in and out ----------
+    latency = None
+    if rank == 0 and world == 1 and not args.no_latency:
+        from physics_informed_reinforcement_learning_b200 import MeentIndex, random_bunch_init
+        env = MeentIndex(n_cells=args.n_cells, wavelength=args.wavelength, desired_angle=args.angle, order=args.order,
+                         thickness=args.thickness)
+        np.random.seed(42)
+        struct = random_bunch_init(args.n_cells)
+        for _ in range(5):
+            env.get_efficiency(struct)
+        ts = []
+        for i in range(50):
+            struct[(37 * i) % args.n_cells] *= -1.0           # one flip per call, like MeentIndex.step
+            t0 = time.perf_counter()
+            env.get_efficiency(struct)
+            ts.append(time.perf_counter() - t0)
+        ts.sort()
+        latency = {"config": "configs[0]: one structure per call through MeentIndex.get_efficiency (host array in, float out)",
+                   "gpu_ms_b1": ts[len(ts) // 2] * 1e3, "gpu_ms_b1_min": ts[0] * 1e3,
+                   "cpu_ms_b1": (1e3 / cpu["single_core_evals_per_s"]) if cpu else None,
+                   "cpu_kind": "oracle port, one core, one call"}
+
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -349,14 +430,17 @@ def run_b200(args):
     # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/ncu_traffic.json), scaled to
     # this run's structures per launch; null when no capture of that kernel is committed
     traffic = None
+    pipe_pct = None
     try:
         with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as fh:
             t = json.load(fh).get(name)
         if t:
             traffic = (t["dram_read_bytes"] + t["dram_write_bytes"]) * structs_per_launch / t["structures_per_launch"]
+            pipe_pct = t.get("fp64_pipe_pct")
     except (OSError, ValueError, KeyError):
         traffic = None
-    roofline = {"bound": "tensor", "kernel": name, "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+    # "fp64": the bound is the FP64 FMA pipe (no tensor instruction on this path; the contract's enum has no FP64 member)
+    roofline = {"bound": "fp64", "kernel": name, "fp64_pipe_pct": pipe_pct, "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
                 "frac": achieved / fp64_peak, "traffic": traffic,
                 "algorithmic_bytes_per_launch": (args.n_cells + 8) * structs_per_launch,
                 "peak_source": "FP64: cuBLAS DGEMM 8192^3 best of 6 measured in this run (MEASURED_PEAKS.json has no FP64 row)",
@@ -366,13 +450,15 @@ def run_b200(args):
                          "frac": value / world * f_alg(ff) / 1e12 / fp64_peak},
                 "stages_ms_per_step": {k: v[0] / args.steps for k, v in stage.items()},
                 "stage_timing": "serial pass after the timed region (sub-chunk pipeline off): each kernel alone between two CUDA events"}
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": n_warm,
             "ms_per_step": job_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "n_cells": args.n_cells, "order": args.order, "batch_per_gpu": args.batch,
+            "config": {"workload": workload_name(args), "n_cells": args.n_cells, "order": args.order, "batch_per_gpu": args.batch,
                        "global_batch": args.batch * world, "wavelength_nm": args.wavelength, "angle_deg": args.angle,
-                       "thickness_nm": args.thickness, "parallelism": f"structures sharded over {world} GPU(s)",
-                       "l2": "384 MiB flush between timed iterations; workspaces (3 x 215 MB) exceed L2"},
+                       "thickness_nm": args.thickness, "chunk": max_batch,
+                       "parallelism": f"structures sharded over {world} GPU(s)"
+                                      + ("; one NCCL all_gather of the float64 efficiencies per step, inside the timed region" if world > 1 else ""),
+                       "l2": "384 MiB flush between timed iterations; workspaces exceed L2"},
             "e2e": {"value": total_evals / e2e_job_s, "unit": UNIT,
                     "h2d_bytes_per_step": int(hp.nbytes + 32), "d2h_bytes_per_step": int(he.nbytes + hs.nbytes),
                     "ms_per_step": e2e_job_s / args.steps * 1e3},
@@ -382,6 +468,10 @@ def run_b200(args):
         line["cpu_baseline"] = cpu
     if grad_info is not None:
         line["adjoint_grad"] = grad_info
+    if strong is not None:
+        line["strong"] = strong
+    if latency is not None:
+        line["latency"] = latency
     emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -424,6 +514,11 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=10.0, help="seconds of wall time for the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-grad", action="store_true", help="skip the adjoint-gradient leg")
+    ap.add_argument("--max-batch", type=int, default=0, help="structures per internal chunk (0: batch, or 4096 beyond order 60)")
+    ap.add_argument("--strong-batch", type=int, default=0, help="fixed GLOBAL batch of the strong-scaling leg (0: --batch)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1)")
+    ap.add_argument("--no-latency", action="store_true", help="skip the single-call latency leg (N = 1)")
+    ap.add_argument("--no-sync-after-flush", action="store_true", help="experiment: no device sync between the (untimed) L2 flush and the timed step")
     args = ap.parse_args()
     quiet_stdout()
     if args.impl == "reference":

@@ -13,13 +13,20 @@ def shard_range(total: int, rank: int, world: int):
     return lo, hi
 
 
-def gather_efficiencies(local_eff, total: int, group=None):
-    """all_gather of ragged contiguous shards -> full [total] tensor on every rank (same device / dtype)."""
+def gather_efficiencies(local_eff, total: int, group=None, out=None):
+    """all_gather of contiguous shards -> full [total] tensor on every rank (same device / dtype).
+    Equal shards (total % world == 0) take ONE ``all_gather_into_tensor`` straight into ``out`` (allocated once by the
+    caller when it sits in a timed loop); ragged shards are padded to the longest one."""
     import torch
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()):
         return local_eff
     world = dist.get_world_size(group)
+    if total % world == 0 and local_eff.numel() * world == total:
+        if out is None:
+            out = torch.empty(total, dtype=local_eff.dtype, device=local_eff.device)
+        dist.all_gather_into_tensor(out, local_eff.contiguous(), group=group)
+        return out
     sizes = [shard_range(total, r, world) for r in range(world)]
     maxn = max(hi - lo for lo, hi in sizes)
     pad = torch.zeros(maxn, dtype=local_eff.dtype, device=local_eff.device)
