@@ -105,15 +105,18 @@ struct CkPipe {
     const uint32_t mb = mbl + 8u * (rnd & 1u);
     if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes) : "memory");
     const uint32_t parity = (rnd >> 1) & 1u;
-    asm volatile(
-        "{\n\t.reg .pred p;\n"
-        "CK_WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra CK_DONE_%=;\n\t"
-        "bra CK_WAIT_%=;\n"
-        "CK_DONE_%=:\n\t}"
-        ::"r"(mb), "r"(parity)
-        : "memory");
+    uint32_t done = 0;
+    int spins = 0;
+    do {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(mb), "r"(parity)
+          : "memory");
+      if (!done && ++spins > (1 << 24)) __trap();      // a lost round would otherwise hang the GPU (protocol error, never data dependent)
+    } while (!done);
     ++rnd;
   }
 };
@@ -166,11 +169,9 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
   const int FFR = P.ff, N = P.N, z = 2 * N, nc = P.n_cells;
   double* cre = sm + S::cre;
   double* cim = sm + S::cim;
-  double* pvec = sm + S::pvec;
   double* pinvA = sm + S::pinvA;
   double* disA = sm + S::disA;
   double* betaS = sm + S::betaS;
-  double* kkp = sm + S::kkp;
   int* ints = reinterpret_cast<int*>(sm + S::ints);
   double* red = sm + S::red;
   double* LT = sm + S::LT;
@@ -184,13 +185,8 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
   const int til = act ? tid / TC : TRL - 1;
   const int tj = act ? tid % TC : TC - 1;
   const int ti = crank * TRL + til;
-  uint32_t rb[NCTA];                                     // shared::cluster address of sm[] in every CTA of the cluster
-#pragma unroll
-  for (int r = 0; r < NCTA; ++r) rb[r] = ck_mapa(ck_smem_u32(sm), (uint32_t)r);
-  auto bcast = [&](int off, double v) {
-#pragma unroll
-    for (int r = 0; r < NCTA; ++r) ck_st_cluster(rb[r] + 8u * (uint32_t)off, v);
-  };
+  CkPipe<NCTA> pipe;
+  pipe.init(sm, S::mbar, tid);
   auto ltoff = [](int k) { return k * FF - (k * (k - 1)) / 2; };     // column k of the packed factor: entries i = k..FF-1
   double* Xg = cscratch + (size_t)cid * CFrontScratch<C>::doubles + CFrontScratch<C>::X;
   double* Vg = cscratch + (size_t)cid * CFrontScratch<C>::doubles + CFrontScratch<C>::V;
@@ -240,6 +236,22 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
           else t[a][b] = fma(da, basis_toeplitz(pi, pj, N, cre, cim), (i == j) ? ia : 0.0);
         }
     }
+    // Pipelined rounds (CkPipe): column k + 1 is updated FIRST by its owners and sent off, then everybody applies the bulk of
+    // step k while those stores are in flight.  publish_col(k): the owners of column k (tile column KBC) all-gather it into
+    // colbuf[k & 1]; the owner of the pivot adds 1/d and d^-1/2.
+#define CK_LDLT_PUBLISH(KBC, KK)                                                                              \
+  do {                                                                                                        \
+    const int kac_ = (KBC) / C::KA_PER_KB;                                                                    \
+    const int cbo_ = S::colbuf + ((KK) & 1) * FE;                                                             \
+    _Pragma("unroll") for (int a = 0; a < RT; ++a) if (a >= kac_) pipe.pub(cbo_ + ti + TR * a, t[a][KBC]);    \
+    if (ti == (KK) - kac_ * TR) {                                                                             \
+      const double piv_ = t[kac_][KBC];                                                                       \
+      if (!(piv_ > 0.0)) bad = 1;                                                                             \
+      pipe.pub(S::pinvA + (KK), 1.0 / piv_);                                                                  \
+      pipe.pub(S::disA + (KK), rsqrt(piv_));                                                                  \
+    }                                                                                                         \
+  } while (0)
+    if (act && tj == 0) CK_LDLT_PUBLISH(0, 0);
 #pragma unroll
     for (int kb = 0; kb < CT; ++kb) {
       const int ka = kb / C::KA_PER_KB;
@@ -247,39 +259,46 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
       for (int kj = 0; kj < TC; ++kj) {
         const int k = kb * TC + kj;
         if (k >= FFR) break;
-        const int kti = k - ka * TR;
-        const int cbo = S::colbuf + (k & 1) * FE;
-        if (act && tj == kj) {
-#pragma unroll
-          for (int a = 0; a < RT; ++a)
-            if (a >= ka) { const int i = ti + TR * a; if (i >= k) bcast(cbo + i, t[a][kb]); }
-          if (ti == kti) {
-            const double piv = t[ka][kb];
-            if (!(piv > 0.0)) bad = 1;
-            bcast(S::pinvA + k, 1.0 / piv);
-            bcast(S::disA + k, rsqrt(piv));
-          }
-        }
-        ck_cluster_sync();
-        const double* cb = sm + cbo;
+        pipe.wait(8u * (uint32_t)((RT - ka) * TR + 2), tid);
+        const double* cb = sm + S::colbuf + (k & 1) * FE;
         const double p = pinvA[k];
-        double li[RT];
+        double li[RT], cj[CT];
 #pragma unroll
         for (int a = 0; a < RT; ++a)
           if (a >= ka) { const int i = ti + TR * a; li[a] = (i > k) ? -cb[i] * p : 0.0; }
 #pragma unroll
         for (int b = 0; b < CT; ++b)
-          if (b >= kb) {
-            const int j = tj + TC * b;
-            const double cj = (j > k) ? cb[j] : 0.0;
-#pragma unroll
-            for (int a = 0; a < RT; ++a)
-              if (a >= ka) t[a][b] = fma(li[a], cj, t[a][b]);
-          }
+          if (b >= kb) { const int j = tj + TC * b; cj[b] = (j > k) ? cb[j] : 0.0; }
         // unit-lower column k into this CTA's packed copy of L
         for (int i = k + 1 + tid; i < FFR; i += NT) LT[ltoff(k) + (i - k)] = cb[i] * p;
+        __syncthreads();       // every thread of this CTA has consumed round k: the next round may be sent
+        if (k + 1 < FFR && act) {       // look-ahead: column k + 1 first, published before the bulk of the update
+          if (kj + 1 < TC) {
+            if (tj == kj + 1) {
+#pragma unroll
+              for (int a = 0; a < RT; ++a) if (a >= ka) t[a][kb] = fma(li[a], cj[kb], t[a][kb]);
+              cj[kb] = 0.0;
+              CK_LDLT_PUBLISH(kb, k + 1);
+            }
+          } else if (kb + 1 < CT) {
+            if (tj == 0) {
+#pragma unroll
+              for (int a = 0; a < RT; ++a) if (a >= ka) t[a][(kb + 1 < CT) ? kb + 1 : kb] = fma(li[a], cj[(kb + 1 < CT) ? kb + 1 : kb], t[a][(kb + 1 < CT) ? kb + 1 : kb]);
+              cj[(kb + 1 < CT) ? kb + 1 : kb] = 0.0;
+              CK_LDLT_PUBLISH(((kb + 1 < CT) ? kb + 1 : kb), k + 1);
+            }
+          }
+        }
+#pragma unroll
+        for (int b = 0; b < CT; ++b)
+          if (b >= kb) {
+#pragma unroll
+            for (int a = 0; a < RT; ++a)
+              if (a >= ka) t[a][b] = fma(li[a], cj[b], t[a][b]);
+          }
       }
     }
+#undef CK_LDLT_PUBLISH
     ck_cluster_sync();     // every CTA has read the last column before phase 2 publishes into the same buffer
     CK_PHASE(1);
     // =========================== phase 2: E -> -E^-1 by symmetric sweeps (column k all-gathered), B' ===========================
@@ -294,6 +313,23 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
           else t[a][b] = fma(de, basis_toeplitz(i, j, N, cre, cim), (i == j) ? eg : 0.0);
         }
     }
+    // published column: d - 1 at the pivot (u_k = -(d - 1) p = p - 1 and v_k = d - 1 then need no special case on the reader
+    // side); the pivot owner adds 1/d.  Same look-ahead pipeline as phase 1.
+#define CK_SWEEP_PUBLISH(KBC, KK)                                                                             \
+  do {                                                                                                        \
+    const int kac_ = (KBC) / C::KA_PER_KB;                                                                    \
+    const int cbo_ = S::colbuf + ((KK) & 1) * FE;                                                             \
+    _Pragma("unroll") for (int a = 0; a < RT; ++a) {                                                          \
+      const int i_ = ti + TR * a;                                                                             \
+      pipe.pub(cbo_ + i_, (i_ == (KK)) ? t[a][KBC] - 1.0 : t[a][KBC]);                                        \
+    }                                                                                                         \
+    if (ti == (KK) - kac_ * TR) {                                                                             \
+      const double piv_ = t[kac_][KBC];                                                                       \
+      if (!(piv_ > 0.0)) bad = 1;                                                                             \
+      pipe.pub(S::scal + ((KK) & 1) * 4, 1.0 / piv_);                                                         \
+    }                                                                                                         \
+  } while (0)
+    if (act && tj == 0) CK_SWEEP_PUBLISH(0, 0);
 #pragma unroll
     for (int kb = 0; kb < CT; ++kb) {
       const int ka = kb / C::KA_PER_KB;
@@ -302,32 +338,41 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
         const int k = kb * TC + kj;
         if (k >= FFR) break;
         const int kti = k - ka * TR;
-        const int cbo = S::colbuf + (k & 1) * FE;
-        const int sco = S::scal + (k & 1) * 4;
-        if (act && tj == kj) {
-#pragma unroll
-          for (int a = 0; a < RT; ++a) { const int i = ti + TR * a; bcast(cbo + i, (i == k) ? t[a][kb] - 1.0 : t[a][kb]); }
-          if (ti == kti) {
-            const double piv = t[ka][kb];
-            if (!(piv > 0.0)) bad = 1;
-            bcast(sco, 1.0 / piv);
-          }
-        }
-        ck_cluster_sync();
-        const double* cb = sm + cbo;
-        const double p = sm[sco];
-        double u[RT];
+        pipe.wait(8u * (uint32_t)(FF + 1), tid);
+        const double* cb = sm + S::colbuf + (k & 1) * FE;
+        const double p = sm[S::scal + (k & 1) * 4];
+        double u[RT], v[CT];
 #pragma unroll
         for (int a = 0; a < RT; ++a) u[a] = -cb[ti + TR * a] * p;
 #pragma unroll
-        for (int b = 0; b < CT; ++b) {
-          const double v = cb[tj + TC * b];
+        for (int b = 0; b < CT; ++b) v[b] = cb[tj + TC * b];
+        __syncthreads();       // round k consumed by every thread of this CTA
+        if (k + 1 < FFR && act) {
+          if (kj + 1 < TC) {
+            if (tj == kj + 1) {
 #pragma unroll
-          for (int a = 0; a < RT; ++a) t[a][b] = fma(u[a], v, t[a][b]);
+              for (int a = 0; a < RT; ++a) t[a][kb] = fma(u[a], v[kb], t[a][kb]);
+              v[kb] = 0.0;
+              CK_SWEEP_PUBLISH(kb, k + 1);
+            }
+          } else if (kb + 1 < CT) {
+            if (tj == 0) {
+#pragma unroll
+              for (int a = 0; a < RT; ++a) t[a][(kb + 1 < CT) ? kb + 1 : kb] = fma(u[a], v[(kb + 1 < CT) ? kb + 1 : kb], t[a][(kb + 1 < CT) ? kb + 1 : kb]);
+              v[(kb + 1 < CT) ? kb + 1 : kb] = 0.0;
+              CK_SWEEP_PUBLISH(((kb + 1 < CT) ? kb + 1 : kb), k + 1);
+            }
+          }
         }
+#pragma unroll
+        for (int b = 0; b < CT; ++b)
+#pragma unroll
+          for (int a = 0; a < RT; ++a) t[a][b] = fma(u[a], v[b], t[a][b]);
         if (ti == kti && tj == kj) t[ka][kb] = -p;
       }
     }
+#undef CK_SWEEP_PUBLISH
+    ck_cluster_sync();     // phase boundary: every CTA has left the pipelined rounds
     if (P.Einv && act) {   // adjoint sweep needs E^-1 (original harmonic order)
       double* Eg = P.Einv + (size_t)sidx * FFR * FFR;
 #pragma unroll
@@ -413,6 +458,18 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
     CK_PHASE(3);
     // =========================== phase 4: Householder tridiagonalisation ===========================
     double* tg = P.tri + (size_t)sidx * 2 * FFR;
+    // Two pipelined rounds per step: (A) column k of the trailing matrix -> colbuf[k & 1] of every CTA, (B) p = beta C22 v and
+    // the partial dot products v . p -> pvec[k & 1], kkp[k & 1].  After round B the owners of column k + 1 apply the rank-2
+    // update to that column first and send round A of step k + 1 before the bulk of the update.
+    // publish_x(k): owners of column k (tile column KBC) send rows of the blocks a >= ka(k); the diagonal goes to tri.
+#define CK_HH_PUBLISH(KBC, KK)                                                                                \
+  do {                                                                                                        \
+    const int kac_ = (KBC) / C::KA_PER_KB;                                                                    \
+    const int xbo_ = S::colbuf + ((KK) & 1) * FE;                                                             \
+    _Pragma("unroll") for (int a = 0; a < RT; ++a) if (a >= kac_) pipe.pub(xbo_ + ti + TR * a, t[a][KBC]);    \
+    if (ti == (KK) - kac_ * TR) tg[KK] = t[kac_][KBC];                                                        \
+  } while (0)
+    if (FFR >= 3 && act && tj == 0) CK_HH_PUBLISH(0, 0);
 #pragma unroll
     for (int kb = 0; kb < CT; ++kb) {
       const int ka = kb / C::KA_PER_KB;
@@ -420,15 +477,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
       for (int kj = 0; kj < TC; ++kj) {
         const int k = kb * TC + kj;
         if (k > FFR - 3) break;
-        const int kti = k - ka * TR;
-        const int xbo = S::colbuf + (k & 1) * FE;
         double* c2 = sm + S::c2buf + (k & 1) * FE;      // column k+1 of the trailing matrix (rows > k of this CTA)
-        if (act && tj == kj) {
-#pragma unroll
-          for (int a = 0; a < RT; ++a)
-            if (a >= ka) { const int i = ti + TR * a; if (i > k) bcast(xbo + i, t[a][kb]); }
-          if (ti == kti) tg[k] = t[ka][kb];
-        }
         if (act) {                               // column k+1 sits in this column block, or is the first of the next one
           const int kbn = (kb + 1 < CT) ? kb + 1 : kb;   // constant after unrolling
           if (kj + 1 < TC) {
@@ -443,8 +492,8 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
               if (a >= ka) { const int i = ti + TR * a; if (i > k) c2[i] = t[a][kbn]; }
           }
         }
-        ck_cluster_sync();
-        const double* xb = sm + xbo;
+        pipe.wait(8u * (uint32_t)((RT - ka) * TR), tid);
+        const double* xb = sm + S::colbuf + (k & 1) * FE;
         // (A) s = |x|^2 -> alpha, v0, beta, redundantly in every warp;  (B) partial row sums of C22 x with the UN-normalised
         // column: v = x - alpha e_{k+1} gives C22 v = C22 x - alpha C22[:, k+1], corrected by the row-sum threads
         double s = 0.0;
@@ -476,63 +525,97 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
         s = warp_sum(s);
         const double x0 = xb[k + 1];
         const double tail2 = s - x0 * x0;
-        if (!(tail2 > 0.0)) {                 // nothing to annihilate (uniform over the cluster)
+        const bool skip = !(tail2 > 0.0);     // nothing to annihilate (uniform over the cluster)
+        double alpha = 0.0, v0 = 0.0, beta = 0.0;
+        if (!skip) {
+          alpha = -copysign(sqrt(s), x0);
+          v0 = x0 - alpha;
+          beta = 1.0 / (s - alpha * x0);
+#pragma unroll
+          for (int a = 0; a < RT; ++a)
+            if (a >= ka) { if (ti + TR * a == k + 1) vi[a] = v0; }
+#pragma unroll
+          for (int b = 0; b < CT; ++b)
+            if (b >= kb) { if (tj + TC * b == k + 1) vj[b] = v0; }
+        }
+        __syncthreads();       // partial sums visible; round A of this step consumed by every thread of this CTA
+        double wi[RT], wj[CT];
+        if (skip) {
           if (tid == 0) { betaS[k] = 0.0; if (crank == 0) tg[FFR + k] = x0; }
-          continue;
+#pragma unroll
+          for (int a = 0; a < RT; ++a) { wi[a] = 0.0; vi[a] = 0.0; }
+#pragma unroll
+          for (int b = 0; b < CT; ++b) { wj[b] = 0.0; vj[b] = 0.0; }
+        } else {
+          // rows of this CTA: p = beta C22 v (four lanes per row), all-gathered; partial v . p per warp -> every CTA
+          const int pvo = S::pvec + (k & 1) * FE, kko = S::kkp + (k & 1) * 32;
+          if (tid < C::RS_THREADS) {
+            const int lr = tid >> 2, sub = tid & 3;
+            double acc = 0.0;
+            if (lr < LROWS) {
+#pragma unroll
+              for (int c = 0; c < (TC + 3) / 4; ++c) { const int cc = sub + 4 * c; if (cc < TC) acc += red[lr * RW + cc]; }
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            double contrib = 0.0;
+            const int r = crank * TRL + (lr % TRL) + TR * (lr / TRL);
+            if (lr < LROWS && sub == 0 && r > k && r < FFR) {
+              acc = fma(-alpha, c2[r], acc);                    // C22 v = C22 x - alpha C22[:, k+1]
+              const double vr = (r == k + 1) ? v0 : xb[r];
+              const double pr_ = beta * acc;
+              pipe.pub(pvo + r, pr_);
+              contrib = pr_ * vr;
+              __stcg(&Vg[(size_t)k * FF + r], vr);              // reflector -> L2-resident scratch (read back in phase 5)
+            }
+            contrib = warp_sum(contrib);
+            if (lane == 0) pipe.pub(kko + crank * C::RS_WARPS + warp, contrib);
+          }
+          if (tid == 0) { betaS[k] = beta; if (crank == 0) tg[FFR + k] = alpha; }
+          pipe.wait(8u * (uint32_t)((FFR - 1 - k) + NCTA * C::RS_WARPS), tid);
+          const double* pvec = sm + pvo;
+          double kk = (lane < NCTA * C::RS_WARPS) ? sm[kko + lane] : 0.0;
+          kk = warp_sum(kk);
+          kk *= 0.5 * beta;
+#pragma unroll
+          for (int a = 0; a < RT; ++a)
+            if (a >= ka) { const int i = ti + TR * a; wi[a] = (i > k && i < FFR) ? fma(-kk, vi[a], pvec[i]) : 0.0; }
+#pragma unroll
+          for (int b = 0; b < CT; ++b)
+            if (b >= kb) { const int j = tj + TC * b; wj[b] = (j > k && j < FFR) ? fma(-kk, vj[b], pvec[j]) : 0.0; }
         }
-        const double alpha = -copysign(sqrt(s), x0);
-        const double v0 = x0 - alpha;
-        const double beta = 1.0 / (s - alpha * x0);
+        // look-ahead: column k + 1 gets its rank-2 update first and is sent as round A of step k + 1
+        if (k + 1 <= FFR - 3 && act) {
+          if (kj + 1 < TC) {
+            if (tj == kj + 1) {
 #pragma unroll
-        for (int a = 0; a < RT; ++a)
-          if (a >= ka) { if (ti + TR * a == k + 1) vi[a] = v0; }
+              for (int a = 0; a < RT; ++a) if (a >= ka) t[a][kb] = fma(-vi[a], wj[kb], fma(-wi[a], vj[kb], t[a][kb]));
+              wj[kb] = 0.0; vj[kb] = 0.0;
+              CK_HH_PUBLISH(kb, k + 1);
+            }
+          } else if (kb + 1 < CT) {
+            if (tj == 0) {
 #pragma unroll
-        for (int b = 0; b < CT; ++b)
-          if (b >= kb) { if (tj + TC * b == k + 1) vj[b] = v0; }
-        __syncthreads();
-        // rows of this CTA: p = beta C22 v (four lanes per row), all-gathered; partial v . p per warp -> every CTA
-        if (tid < C::RS_THREADS) {
-          const int lr = tid >> 2, sub = tid & 3;
-          double acc = 0.0;
-          if (lr < LROWS) {
-#pragma unroll
-            for (int c = 0; c < (TC + 3) / 4; ++c) { const int cc = sub + 4 * c; if (cc < TC) acc += red[lr * RW + cc]; }
+              for (int a = 0; a < RT; ++a)
+                if (a >= ka) t[a][(kb + 1 < CT) ? kb + 1 : kb] = fma(-vi[a], wj[(kb + 1 < CT) ? kb + 1 : kb], fma(-wi[a], vj[(kb + 1 < CT) ? kb + 1 : kb], t[a][(kb + 1 < CT) ? kb + 1 : kb]));
+              wj[(kb + 1 < CT) ? kb + 1 : kb] = 0.0; vj[(kb + 1 < CT) ? kb + 1 : kb] = 0.0;
+              CK_HH_PUBLISH(((kb + 1 < CT) ? kb + 1 : kb), k + 1);
+            }
           }
-          acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-          acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-          double contrib = 0.0;
-          const int r = crank * TRL + (lr % TRL) + TR * (lr / TRL);
-          if (lr < LROWS && sub == 0 && r > k && r < FFR) {
-            acc = fma(-alpha, c2[r], acc);                    // C22 v = C22 x - alpha C22[:, k+1]
-            const double vr = (r == k + 1) ? v0 : xb[r];
-            const double pr_ = beta * acc;
-            bcast(S::pvec + r, pr_);
-            contrib = pr_ * vr;
-            __stcg(&Vg[(size_t)k * FF + r], vr);              // reflector -> L2-resident scratch (read back in phase 5)
-          }
-          contrib = warp_sum(contrib);
-          if (lane == 0) bcast(S::kkp + crank * C::RS_WARPS + warp, contrib);
         }
-        if (tid == 0) { betaS[k] = beta; if (crank == 0) tg[FFR + k] = alpha; }
-        ck_cluster_sync();
-        double kk = (lane < NCTA * C::RS_WARPS) ? kkp[lane] : 0.0;
-        kk = warp_sum(kk);
-        kk *= 0.5 * beta;
-        double wi[RT];
+        if (!skip) {
 #pragma unroll
-        for (int a = 0; a < RT; ++a)
-          if (a >= ka) { const int i = ti + TR * a; wi[a] = (i > k && i < FFR) ? fma(-kk, vi[a], pvec[i]) : 0.0; }
+          for (int b = 0; b < CT; ++b)
+            if (b >= kb) {
 #pragma unroll
-        for (int b = 0; b < CT; ++b)
-          if (b >= kb) {
-            const int j = tj + TC * b;
-            const double wjb = (j > k && j < FFR) ? fma(-kk, vj[b], pvec[j]) : 0.0;
-#pragma unroll
-            for (int a = 0; a < RT; ++a)
-              if (a >= ka) t[a][b] = fma(-vi[a], wjb, fma(-wi[a], vj[b], t[a][b]));
-          }
+              for (int a = 0; a < RT; ++a)
+                if (a >= ka) t[a][b] = fma(-vi[a], wj[b], fma(-wi[a], vj[b], t[a][b]));
+            }
+        }
       }
     }
+#undef CK_HH_PUBLISH
+    ck_cluster_sync();     // phase boundary
     // trailing 2x2 block of the real harmonics
     if (act) {
 #pragma unroll
@@ -552,6 +635,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
 #pragma unroll
       for (int b = 0; b < CT; ++b) t[a][b] = (ti + TR * a == tj + TC * b) ? 1.0 : 0.0;
     ck_cluster_sync();       // reflectors of every CTA are visible in L2
+    double* pvec = sm + S::pvec;
     {
       double vn[CT];         // reflector of the NEXT step, prefetched from L2 under the current one
       {
@@ -660,8 +744,8 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
       }
     }
     // ---- status, next structure ----
-    if (__syncthreads_or(bad)) { if (tid == 0) ck_st_cluster_i32(rb[0] + 8u * S::ints + 4u * (1 + crank), 1); }
-    else if (tid == 0) ck_st_cluster_i32(rb[0] + 8u * S::ints + 4u * (1 + crank), 0);
+    if (__syncthreads_or(bad)) { if (tid == 0) ck_st_cluster_i32(pipe.rb[0] + 8u * S::ints + 4u * (1 + crank), 1); }
+    else if (tid == 0) ck_st_cluster_i32(pipe.rb[0] + 8u * S::ints + 4u * (1 + crank), 0);
     ck_cluster_sync();
     if (crank == 0 && tid == 0) {
       int anybad = 0;
@@ -670,7 +754,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_front(KParams P, double* __restri
       P.wstatus[sidx] = anybad ? PIRL_ST_NPD : 0;
       const int nxt = P.queue ? nclusters + atomicAdd(P.queue, 1) : sidx + nclusters;
 #pragma unroll
-      for (int r = 0; r < NCTA; ++r) ck_st_cluster_i32(rb[r] + 8u * S::ints, nxt);
+      for (int r = 0; r < NCTA; ++r) ck_st_cluster_i32(pipe.rb[r] + 8u * S::ints, nxt);
     }
     ck_cluster_sync();
     sidx = ints[0];

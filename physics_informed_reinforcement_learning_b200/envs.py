@@ -13,6 +13,7 @@
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -125,7 +126,8 @@ class VectorDeflectorEnv:
     """B independent MeentIndex envs advanced by one batched RCWA launch per step (device resident)."""
 
     def __init__(self, num_envs, n_cells=256, wavelength=1100, desired_angle=60, order=40, thickness=325,
-                 max_episode_steps=128, device=None, backend: RCWABatch | None = None):
+                 max_episode_steps=128, device=None, backend: RCWABatch | None = None, data_dir=None,
+                 check_status_every=0):
         import torch
         self.torch = torch
         self.B, self.n_cells = int(num_envs), int(n_cells)
@@ -141,6 +143,20 @@ class VectorDeflectorEnv:
         self.best_eff = torch.zeros(self.B, dtype=torch.float64, device=dev)
         self.best_patterns = torch.ones(self.B, self.n_cells, dtype=torch.int8, device=dev)
         self.elapsed = np.zeros(self.B, dtype=np.int64)
+        # best structure over ALL episodes of all envs (BestRecorder keeps it per episode, wrappers.py:10-16, and the
+        # reference's callback writes it at every episode end, main.py:76-85): survives the auto-reset
+        self.global_best_eff = torch.full((), -1.0, dtype=torch.float64, device=dev)
+        self.global_best_pattern = torch.ones(self.n_cells, dtype=torch.int8, device=dev)
+        self.episodes_done = 0
+        # StructureWriter (utils.py:36-82): the structure is written at every reset as <eff*100>_<timestamp>.npy
+        self.data_dir = data_dir
+        if data_dir is not None:
+            os.makedirs(os.path.join(data_dir, "MeentIndex"), exist_ok=True)
+        # solver status words (non-converged eigensolve, non-finite result, not positive definite): checked every N steps
+        # (0 = never on the step path; check_status() on demand).  The reference raises LinAlgError instead.
+        self.check_status_every = int(check_status_every)
+        self._status_acc = torch.zeros((), dtype=torch.int32, device=dev)
+        self._steps = 0
         rows, _ = self.backend._params(1, float(wavelength), float(desired_angle), float(thickness), None)
         self.params = torch.from_numpy(rows).to(dev)
         self.observation_space = _Box(low=-1., high=1., shape=(self.n_cells,), dtype=np.float64)
@@ -151,7 +167,40 @@ class VectorDeflectorEnv:
         return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
 
     def _evaluate(self, patterns):
-        return self.backend.evaluate(patterns, params=self.params)
+        eff, st = self.backend.evaluate(patterns, params=self.params, return_status=True)
+        self._status_acc |= st.max() if st.numel() else 0       # device side, no sync
+        return eff
+
+    def check_status(self):
+        """Raise if any evaluation since the last check set a solver status bit (one device->host read)."""
+        bits = int(self._status_acc.item())
+        self._status_acc.zero_()
+        if bits:
+            raise FloatingPointError(f"RCWA solver status bits {bits:#x} set (1 = eigensolver not converged, 2 = non-finite "
+                                     f"efficiency, 4 = permittivity matrices not positive definite)")
+
+    def _fold_global_best(self, idx=None):
+        """Fold the per-episode bests (all envs, or the envs ``idx`` that are about to be reset) into the global best."""
+        torch = self.torch
+        be = self.best_eff if idx is None else self.best_eff[idx]
+        bp = self.best_patterns if idx is None else self.best_patterns[idx]
+        m, j = be.max(dim=0)
+        better = m > self.global_best_eff
+        self.global_best_eff = torch.where(better, m, self.global_best_eff)
+        self.global_best_pattern = torch.where(better, bp[j], self.global_best_pattern)
+
+    def best(self):
+        """(efficiency, structure float64 [n]) of the best structure seen so far, finished and running episodes alike."""
+        self._fold_global_best()
+        return float(self.global_best_eff.item()), self.global_best_pattern.to(self.torch.float64).cpu().numpy()
+
+    def _write_structures(self, idx, eff, patterns):
+        from datetime import datetime
+        stamp = datetime.now().strftime('%Y%m%d-%H%M%S')
+        e, p = eff.cpu().numpy(), patterns.cpu().numpy().astype(np.float64)
+        for q, i in enumerate(idx):
+            name = f'{e[q] * 100:.6f}'.replace('.', '-') + '_' + stamp + f'_e{int(i)}'
+            np.save(os.path.join(self.data_dir, "MeentIndex", name), p[q])
 
     def _host_init(self, count):
         if self.n_cells != 256:
@@ -187,6 +236,8 @@ class VectorDeflectorEnv:
             self.best_eff[tidx] = eff
             self.best_patterns[tidx] = init
         self.elapsed[idx] = 0
+        if self.data_dir is not None:
+            self._write_structures(idx, eff, init)
         return self.obs()
 
     def step(self, actions, auto_reset=True):
@@ -208,9 +259,20 @@ class VectorDeflectorEnv:
         reward = self.reward.clone()
         obs = self.obs()
         info = {"TimeLimit.truncated": done_np.copy()}
+        self._steps += 1
+        if self.check_status_every and self._steps % self.check_status_every == 0:
+            self.check_status()
         if auto_reset and done_np.any():
+            didx = np.nonzero(done_np)[0]
+            tidx = torch.from_numpy(didx).to(self.device)
             info["terminal_eff"] = self.eff.clone()
-            self.reset(np.nonzero(done_np)[0])
+            # episode results of the envs that finish now (BestRecorder's env.best at episode end, main.py:76-85)
+            info["episode_env"] = didx
+            info["episode_best_eff"] = self.best_eff[tidx].clone()
+            info["episode_best_patterns"] = self.best_patterns[tidx].clone()
+            self._fold_global_best(tidx)
+            self.episodes_done += int(didx.size)
+            self.reset(didx)
             obs = self.obs()
         return obs, reward, torch.from_numpy(done_np).to(self.device), info
 

@@ -80,8 +80,16 @@ class RCWABatch:
             rows[:, j] = c
         return rows, (4 if n > 1 else 0)
 
+    def _check_params(self, params, B):
+        torch = _torch()
+        if (not torch.is_tensor(params) or params.dtype != torch.float64 or params.dim() != 2 or params.shape[1] != 4
+                or params.shape[0] not in (1, B) or not params.is_cuda):
+            raise ValueError(f"params must be a float64 CUDA tensor of shape [1, 4] or [{B}, 4] "
+                             "(rows {wavelength, angle, thickness, n_ridge})")
+        return params.contiguous()
+
     def evaluate(self, patterns, wavelength=1100.0, angle=60.0, thickness=325.0, n_ridge=None,
-                 return_orders=False, params=None):
+                 return_orders=False, params=None, return_status=False):
         """patterns: torch int8 CUDA tensor [B, n_cells] of +-1.  Returns eff [B] float64 (CUDA), and with
         ``return_orders`` also (de_r3, de_t3, status) -- rows are de[N-1], de[N], de[N+1].
         Asynchronous on the current torch stream; no host<->device copies of bulk data."""
@@ -97,6 +105,7 @@ class RCWABatch:
             rows, stride = self._params(B, wavelength, angle, thickness, n_ridge)
             params = torch.from_numpy(rows).to(dev, non_blocking=True)
         else:
+            params = self._check_params(params, B)
             stride = 4 if params.shape[0] > 1 else 0
         eff = torch.empty(B, dtype=torch.float64, device=dev)
         st = torch.empty(B, dtype=torch.int32, device=dev)
@@ -112,6 +121,8 @@ class RCWABatch:
         self._keep = (patterns, params)  # keep inputs alive until the stream has consumed them
         if return_orders:
             return eff, r3, t3, st
+        if return_status:
+            return eff, st
         return eff
 
     def evaluate_host(self, patterns, wavelength=1100.0, angle=60.0, thickness=325.0, n_ridge=None,
@@ -156,6 +167,7 @@ class RCWABatch:
             rows, stride = self._params(B, wavelength, angle, thickness, n_ridge)
             params = torch.from_numpy(rows).to(dev, non_blocking=True)
         else:
+            params = self._check_params(params, B)
             stride = 4 if params.shape[0] > 1 else 0
         eff = torch.empty(B, dtype=torch.float64, device=dev)
         grad = torch.empty(B, self.n_cells, dtype=torch.float64, device=dev)
