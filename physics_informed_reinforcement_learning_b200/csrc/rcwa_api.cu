@@ -155,6 +155,8 @@ static int mats_that_fit(size_t budget, size_t vec_bytes, size_t mat_bytes, int 
   return k;
 }
 
+extern "C" int pirl_rcwa_destroy(pirl_handle* h);
+
 extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   if (!cfg || !out) return fail(-1, "null argument");
   if (cfg->order < 1 || cfg->order > 126) return fail(-2, "order must be in [1,126] (rotation column index is 8 bit)");
@@ -172,6 +174,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   CUDA_TRY(cudaGetDeviceProperties(&prop, cfg->device));
 
   pirl_handle* h = new pirl_handle();
+  struct Guard { pirl_handle* h; ~Guard() { if (h) pirl_rcwa_destroy(h); } } guard{h};   // error paths below free everything
   h->cfg = *cfg;
   const int N = cfg->order, ff = 2 * N + 1, nc = cfg->n_cells;
   h->ff = ff;
@@ -354,6 +357,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     if (const char* e = getenv("PIRL_SUBCHUNK")) h->sub_size = atoi(e);
     h->no_rktail = getenv("PIRL_NO_RKTAIL") != nullptr;
   }
+  guard.h = nullptr;
   *out = h;
   return 0;
 }
@@ -538,9 +542,10 @@ static int launch_chunk(pirl_handle* h, KParams P, int Bc, cudaStream_t st, cons
   // a high-priority side stream as soon as its front kernel is done (under the following front / back kernels), and the
   // back kernels (k_apply, tail) follow on the caller's stream, each waiting for its own k_ql.
   int sub = h->sub_size;
-  if (sub < 0) sub = ((h->regtile || h->regfront121) && Bc >= 4 * h->rk_front_grid) ? (Bc + 1) / 2 : 0;
+  if (!(h->regtile || h->regfront121)) sub = 0;   // the generic kernels share per-CTA scratch across launches; the cluster kernels fill the GPU
+  if (sub < 0) sub = (Bc >= 4 * h->rk_front_grid) ? (Bc + 1) / 2 : 0;
   int nsub = (sub > 0) ? (Bc + sub - 1) / sub : 1;
-  if (nsub > pirl_handle::kMaxSub) nsub = pirl_handle::kMaxSub;
+  if (nsub > pirl_handle::kMaxSub) { sub = (Bc + pirl_handle::kMaxSub - 1) / pirl_handle::kMaxSub; nsub = (Bc + sub - 1) / sub; }
   if (nsub <= 1) {
     launch_front(h, P, st);
     launch_ql(h, P, st);
@@ -552,7 +557,7 @@ static int launch_chunk(pirl_handle* h, KParams P, int Bc, cudaStream_t st, cons
     // (one warp per SM, co-resident with two rk_front CTAs: that is why rk_front is capped at 112 registers -- 4 warps x 112
     // + one k_ql warp x 64 registers fill one SM sub-partition exactly), then all k_apply, then all tails on the caller's
     // stream: the last k_ql hides under the k_apply launches of the earlier sub-chunks.
-    const int per = (sub * nsub >= Bc) ? sub : (Bc + nsub - 1) / nsub;
+    const int per = sub;
     KParams Ps[pirl_handle::kMaxSub];
     CUDA_TRY(cudaEventRecord(h->evStart, st));
     for (int c = 0; c < nsub; ++c) {

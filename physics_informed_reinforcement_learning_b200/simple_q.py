@@ -109,6 +109,11 @@ class SimpleQTrainer:
         self.log_dir = log_dir
         self.obs = None
         self.max_efficiency = float("-inf")
+        # best structure over finished AND running episodes of this rank (the env resets its per-episode best on auto-reset;
+        # the reference dumps the best structure at every episode end, main.py:76-85)
+        self.best_eff = float("-inf")
+        self.best_pattern = None
+        self.backlog_warned = False
         self.timers = {"env": 0.0, "act": 0.0, "learn": 0.0}
 
     # --------------------------------------------------------------------------------------------
@@ -218,13 +223,21 @@ class SimpleQTrainer:
             s_next[rows, actions[rows]] = -s_next[rows, actions[rows]]
             self.replay.add(self.obs, actions, reward, s_next, done.to(torch.bool))
             self.obs = nxt
+            if isinstance(info, dict) and "episode_best_eff" in info and info["episode_best_eff"].numel():
+                self._fold_best(info["episode_best_eff"], info["episode_best_patterns"])
             sync(); t2 = time.perf_counter()
             self.timesteps += per_iter
             if self.replay.size * self.world >= cfg.learning_starts:
                 if self.learn_credit_from is None:
                     self.learn_credit_from = self.timesteps - per_iter
+                # one learner update per `timesteps_per_update` sampled timesteps (configs/simple_q.py:71-73), never more
                 owed = (self.timesteps - self.learn_credit_from) // max(cfg.timesteps_per_update, 1) - self.updates
-                for _ in range(int(min(max(owed, 1), cfg.max_updates_per_iter))):
+                if owed > cfg.max_updates_per_iter and not self.backlog_warned and self.rank == 0:
+                    self.backlog_warned = True
+                    print(f"[simple_q] {per_iter} timesteps per iteration owe {owed} learner updates, more than "
+                          f"max_updates_per_iter={cfg.max_updates_per_iter}: the sample-to-update ratio of the reference "
+                          f"is not reached (raise max_updates_per_iter or train_batch_size)", flush=True)
+                for _ in range(int(min(max(owed, 0), cfg.max_updates_per_iter))):
                     losses.append(self.learn())
                 if self.timesteps - self.last_target_sync >= cfg.target_network_update_freq:
                     self.sync_target()
@@ -233,10 +246,11 @@ class SimpleQTrainer:
             self.timers["act"] += t1 - t0; self.timers["env"] += t2 - t1; self.timers["learn"] += t3 - t2
             it += 1
             if log_every and it % log_every == 0 and self.rank == 0:
-                print(f"[simple_q] t={self.timesteps} eps={eps:.3f} max_eff={float(env.best_eff.max()):.4f} "
+                print(f"[simple_q] t={self.timesteps} eps={eps:.3f} max_eff={max(self.best_eff, float(env.best_eff.max())):.4f} "
                       f"loss={float(losses[-1]) if losses else float('nan'):.3e}", flush=True)
         wall = time.perf_counter() - t_start
-        best = env.best_eff.max().to(torch.float64).reshape(1).clone()
+        self._fold_best(env.best_eff, env.best_patterns)          # episodes still running
+        best = torch.tensor([self.best_eff], dtype=torch.float64, device=self.device)
         if self.world > 1:
             dist.all_reduce(best, op=dist.ReduceOp.MAX)
         self.max_efficiency = float(best)
@@ -246,14 +260,57 @@ class SimpleQTrainer:
                 "time_fraction": {k: v / total for k, v in self.timers.items()},
                 "final_loss": float(losses[-1]) if losses else None, "epsilon": epsilon_at(cfg, self.timesteps)}
 
+    def _fold_best(self, effs, patterns):
+        i = int(effs.argmax())
+        e = float(effs[i])
+        if e > self.best_eff:
+            self.best_eff = e
+            self.best_pattern = patterns[i].to(torch.float64).cpu().numpy().copy()
+
     def save_best(self):
-        """main.py:80-85: dump the best structure of this rank as .npy, file name from eff * 100."""
+        """main.py:80-85: dump the best structure seen by this rank (finished and running episodes) as .npy, file name from
+        eff * 100."""
         if not self.log_dir:
             return None
         os.makedirs(self.log_dir, exist_ok=True)
-        i = int(self.env.best_eff.argmax())
-        eff = float(self.env.best_eff[i])
-        name = "w" + str(self.rank) + f"_{eff * 100:.6f}".replace(".", "-")
+        self._fold_best(self.env.best_eff, self.env.best_patterns)
+        name = "w" + str(self.rank) + f"_{self.best_eff * 100:.6f}".replace(".", "-")
         path = os.path.join(self.log_dir, name)
-        np.save(path, self.env.best_patterns[i].to(torch.float64).cpu().numpy())
+        np.save(path, self.best_pattern)
         return path + ".npy"
+
+    # --------------------------------------------------------------------------------------------
+    def save_checkpoint(self, path: str):
+        """Policy, target, optimiser, counters and RNG state (the reference checkpoints through Ray AIR every iteration and
+        at the end, main.py:176-182).  Every rank holds the same policy; rank 0 writes."""
+        if self.rank != 0:
+            return None
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        state = {"model": self.model.state_dict(), "target": self.target.state_dict(), "optimizer": self.opt.state_dict(),
+                 "timesteps": self.timesteps, "updates": self.updates, "last_target_sync": self.last_target_sync,
+                 "learn_credit_from": self.learn_credit_from, "best_eff": self.best_eff, "best_pattern": self.best_pattern,
+                 "gen_state": self.gen.get_state(), "torch_rng": torch.get_rng_state(), "numpy_rng": np.random.get_state(),
+                 "config": dataclasses.asdict(self.cfg)}
+        tmp = path + ".tmp"
+        torch.save(state, tmp)
+        os.replace(tmp, path)
+        return path
+
+    def load_checkpoint(self, path: str, weights_only: bool = False):
+        """Resume (``--transfer_ckpt`` of the reference, main.py:163-164).  ``weights_only`` loads the two networks and leaves
+        optimiser, counters and exploration schedule fresh (transfer to another wavelength / angle)."""
+        state = torch.load(path, map_location=self.device, weights_only=False)
+        self.model.load_state_dict(state["model"])
+        self.target.load_state_dict(state.get("target", state["model"]))
+        if weights_only:
+            return state
+        self.opt.load_state_dict(state["optimizer"])
+        self.timesteps, self.updates = int(state["timesteps"]), int(state["updates"])
+        self.last_target_sync, self.learn_credit_from = state["last_target_sync"], state["learn_credit_from"]
+        self.best_eff, self.best_pattern = state["best_eff"], state["best_pattern"]
+        self.gen.set_state(state["gen_state"].cpu())
+        torch.set_rng_state(state["torch_rng"].cpu())
+        np.random.set_state(state["numpy_rng"])
+        self._graph = None                # the captured learner graph holds the old parameter values' addresses: still valid,
+        self._graph_warmup = 0            # but re-capture keeps the optimiser state and the graph consistent
+        return state

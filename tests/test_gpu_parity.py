@@ -376,3 +376,91 @@ def test_register_tile_paths_against_shared_memory_kernels_and_pipeline_settings
         # lossless structure: the three reported orders never exceed unity and the efficiencies are non-negative
         assert float(e_auto.min()) >= 0.0 and float((r3.sum(1) + t3.sum(1)).max()) <= 1.0 + 1e-9
         be.close(); ref.close()
+
+
+def _oracle_pool_eval(pats, wl, ang, order, thick):
+    """All host cores: the order-100 oracle costs 0.1-0.2 s per structure."""
+    from oracle import cpu_pool
+    pool = cpu_pool.OraclePool()
+    try:
+        eff, _ = pool.run(pats, wl, ang, order, thick)
+    finally:
+        pool.close()
+    return eff
+
+
+def test_config_c5_order100_256_patterns_vs_oracle(pkg, torch_mod):
+    """BASELINE config 5 (order 100, ff = 201, 512 cells) on the thread-block-cluster kernels: 256 patterns -- random, and
+    8- / 16- / 32-pixel blocks so that efficiencies span 0 ... 0.9 -- against the oracle, all three reported orders of a
+    subset, and the same batch through the generic shared-memory kernels (PIRL_NO_CLUSTER=1), an independent implementation."""
+    torch = torch_mod
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(5)
+    n, order, B = 512, 100, 256
+    pats = (rng.integers(0, 2, (B, n)) * 2 - 1).astype(np.int8)
+    for i, blk in ((1, 8), (2, 16), (3, 32)):
+        pats[i::4] = np.repeat(rng.integers(0, 2, (B // 4, n // blk)) * 2 - 1, blk, axis=1)
+    be = pkg.RCWABatch(n, order, max_batch=B, device=0)
+    be.set_stage_timing(True)
+    eff, r3, t3, st = be.evaluate(torch.from_numpy(pats).cuda(), return_orders=True)
+    torch.cuda.synchronize()
+    times = be.stage_times()
+    be.set_stage_timing(False)
+    assert int(st.abs().sum()) == 0
+    assert times["ck_front"][1] == 1 and times["ck_tail"][1] == 1 and times["k_front"][1] == 0     # the cluster kernels ran
+    eff, r3, t3 = eff.cpu().numpy(), r3.cpu().numpy(), t3.cpu().numpy()
+    ref = _oracle_pool_eval(pats, 1100.0, 60.0, order, 325.0)
+    err = np.abs(eff - ref)
+    assert err.max() <= TOL, (int(err.argmax()), err.max())
+    assert err.max() <= 1e-8                           # observed 1e-9 class; the contract is 1e-6
+    assert ref.max() > 0.3                             # the blocky rows reach large efficiencies
+    for i in (0, 1, 2, 3, 77, 130, 255):
+        r = O.evaluate(pats[i].astype(np.float64), 1100.0, 60.0, order, 325.0)
+        assert np.abs(t3[i] - r.de_ti[order - 1:order + 2]).max() <= TOL and np.abs(r3[i] - r.de_ri[order - 1:order + 2]).max() <= TOL
+    os.environ["PIRL_NO_CLUSTER"] = "1"
+    try:
+        gen = pkg.RCWABatch(n, order, max_batch=32, device=0)
+    finally:
+        del os.environ["PIRL_NO_CLUSTER"]
+    e_gen = gen.evaluate_host(pats[:32])
+    assert np.abs(e_gen - eff[:32]).max() <= 1e-8
+    be.close(); gen.close()
+
+
+@pytest.mark.parametrize("n_cells,order", [(256, 50), (256, 61), (300, 77), (512, 88), (512, 103)])
+def test_cluster_path_orders_vs_oracle(pkg, n_cells, order):
+    """Orders 41-59 and 61-103 run the cluster kernels on the identity-padded 208 x 208 tile grid: other paddings than order 100."""
+    rng = np.random.default_rng(order)
+    pats = (rng.integers(0, 2, (24, n_cells)) * 2 - 1).astype(np.int8)
+    pats[::3] = np.repeat(rng.integers(0, 2, (8, -(-n_cells // 16))) * 2 - 1, 16, axis=1)[:, :n_cells]
+    be = pkg.RCWABatch(n_cells, order, max_batch=16, device=0)        # 24 > 16: two chunks
+    wl, ang, thick = 1000.0, 65.0, 300.0
+    eff, r3, t3, st = be.evaluate_host(pats, wl, ang, thick, return_orders=True)
+    assert not st.any()
+    ref = _oracle_pool_eval(pats, wl, ang, order, thick)
+    assert np.abs(eff - ref).max() <= 1e-8, np.abs(eff - ref).max()
+    assert (r3.sum(1) + t3.sum(1)).max() <= 1.0 + 1e-9
+    be.close()
+
+
+def test_cluster_small_variant_matches_register_tile_kernels(pkg, torch_mod):
+    """PIRL_FORCE_CLUSTER=1 routes order 40 through the 84 x 84 instance of the cluster kernels (same code, four CTAs, small
+    tiles): against the single-SM register-tile kernels on 600 structures, work queue and ragged last wave included."""
+    torch = torch_mod
+    rng = np.random.default_rng(8)
+    pats = torch.from_numpy((rng.integers(0, 2, (600, 256)) * 2 - 1).astype(np.int8)).cuda()
+    ref = pkg.RCWABatch(256, 40, max_batch=600, device=0)
+    e_ref, r_ref, t_ref, _ = ref.evaluate(pats, return_orders=True)
+    os.environ["PIRL_FORCE_CLUSTER"] = "1"
+    os.environ["PIRL_NO_REGTILE"] = "1"
+    try:
+        ck = pkg.RCWABatch(256, 40, max_batch=600, device=0)
+    finally:
+        del os.environ["PIRL_FORCE_CLUSTER"], os.environ["PIRL_NO_REGTILE"]
+    ck.set_stage_timing(True)
+    e, r, t, st = ck.evaluate(pats, return_orders=True)
+    torch.cuda.synchronize()
+    times = ck.stage_times()
+    assert int(st.abs().sum()) == 0 and times["ck_front"][1] == 1 and times["ck_tail"][1] == 1
+    assert float((e - e_ref).abs().max()) <= 1e-9 and float((t - t_ref).abs().max()) <= 1e-9 and float((r - r_ref).abs().max()) <= 1e-9
+    ref.close(); ck.close()

@@ -46,11 +46,16 @@ class ToyEnv:
         self.best_patterns[better] = self.patterns[better]
         self.elapsed += 1
         done = self.elapsed >= self.h
+        info = {}
         if done.any():
+            # same contract as VectorDeflectorEnv.step: episode results go to `info`, then the per-episode best is re-seeded
+            info = {"episode_best_eff": self.best_eff[done].clone(), "episode_best_patterns": self.best_patterns[done].clone()}
             self.patterns[done] = 1
             self.eff = self._eff()
+            self.best_eff[done] = self.eff[done]
+            self.best_patterns[done] = self.patterns[done]
             self.elapsed[done] = 0
-        return self.patterns.to(torch.float64), reward, done, {}
+        return self.patterns.to(torch.float64), reward, done, info
 
 
 def test_unet_matches_reference_layout():
@@ -104,6 +109,33 @@ def test_trainer_learns_toy_env():
         obs, r, d, _ = env.step(tr.act(obs, 0.0))
         tot += r
     assert float(tot.mean()) > 0.1
+
+
+def test_best_survives_auto_reset_and_checkpoint_roundtrip(tmp_path):
+    """max_efficiency must not fall when episodes end (the env re-seeds its per-episode best on auto-reset), and a
+    checkpoint restores policy, optimiser, counters and the best structure."""
+    torch.manual_seed(1)
+    env = ToyEnv(8, n=16, horizon=8)
+    cfg = SimpleQConfig(learning_starts=32, train_batch_size=32, epsilon_timesteps=400, target_network_update_freq=64,
+                        replay_capacity=1024)
+    tr = SimpleQTrainer(env, FCNQNet(16, 32), cfg, log_dir=str(tmp_path))
+    seen = []
+    for stop in (8 * 8 * 3, 8 * 8 * 6, 8 * 8 * 6 + 8):          # ... the last stop ends right after a reset of every env
+        seen.append(tr.train(stop)["max_efficiency"])
+    assert seen[0] <= seen[1] <= seen[2] and seen[2] > float(env.best_eff.max()) - 1e-12
+    assert tr.best_pattern is not None and tr.best_pattern.shape == (16,)
+    best_file = tr.save_best()
+    assert np.array_equal(np.load(best_file), tr.best_pattern)
+    ck = tr.save_checkpoint(str(tmp_path / "ckpt.pt"))
+    tr2 = SimpleQTrainer(ToyEnv(8, n=16, horizon=8), FCNQNet(16, 32), cfg)
+    tr2.load_checkpoint(ck)
+    assert (tr2.timesteps, tr2.updates, tr2.best_eff) == (tr.timesteps, tr.updates, tr.best_eff)
+    for a, b in zip(tr.model.parameters(), tr2.model.parameters()):
+        assert torch.equal(a, b)
+    assert tr2.opt.state_dict()["state"][0]["exp_avg"].equal(tr.opt.state_dict()["state"][0]["exp_avg"])
+    tr3 = SimpleQTrainer(ToyEnv(8, n=16, horizon=8), FCNQNet(16, 32), cfg)
+    tr3.load_checkpoint(ck, weights_only=True)
+    assert tr3.timesteps == 0 and all(torch.equal(a, b) for a, b in zip(tr.model.parameters(), tr3.model.parameters()))
 
 
 def _worker(rank, world, port, q):

@@ -34,6 +34,14 @@ def main():
     ap.add_argument("--log_every", type=int, default=50)
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--no_cuda_graph", action="store_true", help="run the learner step eagerly")
+    ap.add_argument("--transfer_ckpt", type=str, default=None,
+                    help="checkpoint written by this script to resume from (main.py:163-164 algo.load_checkpoint)")
+    ap.add_argument("--transfer_weights_only", action="store_true",
+                    help="with --transfer_ckpt: load the networks only (fresh optimiser, counters and exploration schedule)")
+    ap.add_argument("--checkpoint_every", type=int, default=20000,
+                    help="global timesteps between checkpoints <data_dir>/checkpoint.pt (0: only at the end)")
+    ap.add_argument("--write_structures", action="store_true",
+                    help="StructureWriter (utils.py:36-82): dump every reset structure as .npy under <data_dir>/MeentIndex")
     ap.add_argument("--timesteps_per_update", type=int, default=32,
                     help="sampled env steps per learner update (reference: 16 workers x fragment length 2)")
     args = ap.parse_args()
@@ -50,15 +58,25 @@ def main():
     rank = dist.get_rank() if world > 1 else 0
     per_rank = max(args.num_envs // world, 1)
     env = VectorDeflectorEnv(per_rank, n_cells=args.n_cells, wavelength=args.wavelength, desired_angle=args.angle,
-                             order=args.order, thickness=args.thickness, max_episode_steps=args.max_episode_steps, device=local)
+                             order=args.order, thickness=args.thickness, max_episode_steps=args.max_episode_steps, device=local,
+                             data_dir=args.data_dir if args.write_structures else None, check_status_every=64)
     model = {"unet": lambda: ShallowUQNet(args.n_cells), "fcn": lambda: FCNQNet(args.n_cells),
              "fcn_heavy": lambda: FCNQNet(args.n_cells, 1200)}[args.model]()
     loaded = load_pretrained(model, args.pretrained_ckpt)
     trainer = SimpleQTrainer(env, model, SimpleQConfig(seed=args.seed, timesteps_per_update=args.timesteps_per_update, cuda_graph=not args.no_cuda_graph), log_dir=args.data_dir)
-    out = trainer.train(args.train_steps, log_every=args.log_every)
+    if args.transfer_ckpt:
+        trainer.load_checkpoint(args.transfer_ckpt, weights_only=args.transfer_weights_only)
+    ckpt_path = os.path.join(args.data_dir, "checkpoint.pt")
+    out = {}
+    while trainer.timesteps < args.train_steps:       # periodic checkpoints (Ray AIR CheckpointConfig, main.py:176-182)
+        stop = args.train_steps if args.checkpoint_every <= 0 else min(args.train_steps, trainer.timesteps + args.checkpoint_every)
+        out = trainer.train(stop, log_every=args.log_every)
+        trainer.save_checkpoint(ckpt_path)
+    env.check_status()
     path = trainer.save_best()
     if rank == 0:
-        out.update({"world": world, "envs_per_rank": per_rank, "pretrained_loaded": loaded, "best_structure": path})
+        out.update({"world": world, "envs_per_rank": per_rank, "pretrained_loaded": loaded, "best_structure": path,
+                    "checkpoint": ckpt_path})
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
