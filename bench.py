@@ -60,6 +60,7 @@ STAGE_FLOPS_FF3 = {
     "rk_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
     "ck_front": 28.0 / 3.0 + 44.0 / 3.0,       # thread-block-cluster kernels of the large orders: same stages
     "ck_tail": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,
+    "k_smm": 8.0 + 8.0 / 3.0 + 8.0 + 16.0 + 8.0 / 3.0,   # SMM variant of the layer solve: charged with the ETM tail's algorithmic share
 }
 
 
@@ -242,7 +243,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
 
     max_batch = args.max_batch or (args.batch if args.order <= 60 else min(args.batch, 4096))   # workspace chunk (ff = 201: 3.3 MB per structure)
-    be = RCWABatch(args.n_cells, args.order, max_batch=max_batch, device=local_rank)
+    be = RCWABatch(args.n_cells, args.order, max_batch=max_batch, device=local_rank, algo=args.algo)
     d_pats = torch.from_numpy(pats_np).to(dev)
     params_rows, _ = be._params(1, args.wavelength, args.angle, args.thickness, None)
     d_params = torch.from_numpy(params_rows).to(dev)
@@ -339,7 +340,7 @@ def run_b200(args):
 
     # ---- adjoint-gradient leg (not part of `value`): pirl_rcwa_eval_grad on the same batch, device resident ----------
     grad_info = None
-    if not args.no_grad:
+    if not args.no_grad and args.algo == "TMM":
         for _ in range(2):
             be.evaluate_grad(d_pats, params=d_params)
         torch.cuda.synchronize()
@@ -455,7 +456,7 @@ def run_b200(args):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args), "n_cells": args.n_cells, "order": args.order, "batch_per_gpu": args.batch,
                        "global_batch": args.batch * world, "wavelength_nm": args.wavelength, "angle_deg": args.angle,
-                       "thickness_nm": args.thickness, "chunk": max_batch,
+                       "thickness_nm": args.thickness, "chunk": max_batch, "algo": args.algo,
                        "parallelism": f"structures sharded over {world} GPU(s)"
                                       + ("; one NCCL all_gather of the float64 efficiencies per step, inside the timed region" if world > 1 else ""),
                        "l2": "384 MiB flush between timed iterations; workspaces exceed L2"},
@@ -514,6 +515,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=10.0, help="seconds of wall time for the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-grad", action="store_true", help="skip the adjoint-gradient leg")
+    ap.add_argument("--algo", default="TMM", choices=["TMM", "SMM"], help="layer solve: transmittance matrices (default) or S-matrices")
     ap.add_argument("--max-batch", type=int, default=0, help="structures per internal chunk (0: batch, or 4096 beyond order 60)")
     ap.add_argument("--strong-batch", type=int, default=0, help="fixed GLOBAL batch of the strong-scaling leg (0: --batch)")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1)")

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define PIRL_ABI_VERSION 1
+#define PIRL_ABI_VERSION 2
 
 /* status bits reported per structure (0 == ok) */
 #define PIRL_ST_EIG_NOT_CONVERGED 1  /* QL iteration cap / rotation buffer exceeded          */
@@ -44,7 +44,12 @@ typedef struct pirl_cfg {
   int32_t pol;         /* 1 = TM (the only polarisation on this path)                     */
   int32_t max_batch;   /* structures processed per internal chunk (workspace sizing)      */
   int32_t device;      /* CUDA device ordinal                                             */
-  int32_t reserved;
+  int32_t algo;        /* 0 = ETM / 'TMM' (transfer_method.py:4-75, the default of the reference),
+                          1 = SMM: scattering matrices + Redheffer star products
+                              (scattering_method.py:12-73, smm_util.py:15-85, 289-318)        */
+  int32_t precision;   /* 0 = float64 / complex128 (reference precision).  1 is reserved for the
+                          complex64 fast mode of SURVEY.md section 8b and is rejected by this version */
+  int32_t reserved[7]; /* must be zero (room for later fields without another ABI bump)   */
 } pirl_cfg;
 
 typedef struct pirl_handle pirl_handle;

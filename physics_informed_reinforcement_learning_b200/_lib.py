@@ -18,7 +18,8 @@ class PirlCfg(C.Structure):
     _fields_ = [
         ("n_cells", C.c_int32), ("order", C.c_int32),
         ("n_inc", C.c_double), ("n_exit", C.c_double), ("n_groove", C.c_double), ("theta_deg", C.c_double),
-        ("pol", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32), ("reserved", C.c_int32),
+        ("pol", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32), ("algo", C.c_int32),
+        ("precision", C.c_int32), ("reserved", C.c_int32 * 7),
     ]
 
 

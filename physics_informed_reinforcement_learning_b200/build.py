@@ -1,8 +1,9 @@
 """Build the C-ABI CUDA library in-tree with nvcc for sm_100a (no JIT cache: the .so travels with the repo).
 
-Two translation units (compiled to objects under csrc/build/, linked into libpirl_rcwa.so):
+Three translation units (compiled to objects under csrc/build/, linked into libpirl_rcwa.so):
   rcwa_api.cu      C ABI + the single-SM kernels (rcwa_kernels / rcwa_regtile / rcwa_tail2 / rcwa_grad)
   rcwa_cluster.cu  thread-block-cluster kernels for the large orders (rcwa_cluster.cuh)
+  rcwa_smm.cu      scattering-matrix (algo = SMM) layer solve (rcwa_smm.cuh)
 """
 from __future__ import annotations
 
@@ -18,8 +19,9 @@ HEADER = os.path.join("..", "..", "include", "pirl_rcwa.h")
 # source -> files whose change makes its object stale
 UNITS = {
     "rcwa_api.cu": ["rcwa_api.cu", "rcwa_common.cuh", "rcwa_kernels.cuh", "rcwa_regtile.cuh", "rcwa_tail2.cuh",
-                    "rcwa_grad.cuh", "rcwa_cluster.h", HEADER],
+                    "rcwa_grad.cuh", "rcwa_cluster.h", "rcwa_smm.h", HEADER],
     "rcwa_cluster.cu": ["rcwa_cluster.cu", "rcwa_cluster.cuh", "rcwa_cluster_tail.cuh", "rcwa_cluster.h", "rcwa_common.cuh"],
+    "rcwa_smm.cu": ["rcwa_smm.cu", "rcwa_smm.cuh", "rcwa_smm.h", "rcwa_common.cuh"],
 }
 SOURCES = list(UNITS)
 

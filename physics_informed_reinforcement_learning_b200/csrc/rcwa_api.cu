@@ -6,6 +6,7 @@
 #include "rcwa_tail2.cuh"
 #include "rcwa_grad.cuh"
 #include "rcwa_cluster.h"
+#include "rcwa_smm.h"
 #include "../../include/pirl_rcwa.h"
 
 #include <complex>
@@ -67,6 +68,7 @@ struct pirl_handle {
   bool regfront121 = false;   // ff = 121: padded register-tile front kernel, shared-memory kernels behind it
   // thread-block-cluster path (rcwa_cluster.cu): orders whose matrices do not fit one SM
   bool cluster = false; ClusterPlan cplan; double* cscratch = nullptr;
+  SmmPlan smm; double* smm_scratch = nullptr;    // cfg.algo == 1: scattering-matrix layer solve (rcwa_smm.cu)
   bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
   long long launches = 0;
@@ -86,8 +88,8 @@ struct pirl_handle {
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> ev_pending;  // (stage, (start, stop))
 };
 
-static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail", "g_tail", "g_eigback", "ck_front", "ck_tail"};
-static constexpr int kNumStages = 11;
+static const char* kStageNames[] = {"k_front", "k_tridiag", "k_ql", "k_apply", "k_tail", "rk_front", "rk_tail", "g_tail", "g_eigback", "ck_front", "ck_tail", "k_smm"};
+static constexpr int kNumStages = 12;
 
 // register-tile configuration of the headline size (order 40 -> ff = 81 = 9 x 9 threads, 9 x 9 tile each)
 #ifdef PIRL_FRONT_9x9
@@ -164,6 +166,9 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   if (cfg->pol != 1) return fail(-4, "only TM (pol=1) is implemented: it is the only polarisation DeflectorGym evaluates");
   if (cfg->theta_deg != 0.0) return fail(-5, "only normal incidence (theta=0) is implemented (real-symmetric formulation)");
   if (cfg->max_batch < 1) return fail(-6, "max_batch must be >= 1");
+  if (cfg->algo != 0 && cfg->algo != 1) return fail(-10, "algo must be 0 (ETM / TMM) or 1 (SMM)");
+  if (cfg->precision != 0) return fail(-11, "precision 1 (complex64 fast mode) is not implemented: float64 only");
+  for (int r : cfg->reserved) if (r != 0) return fail(-12, "reserved fields of pirl_cfg must be zero");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
@@ -321,6 +326,11 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
       }
     }
   }
+  if (cfg->algo == 1) {
+    CUDA_TRY(smm_plan(ff, N, nc, h->sm_count, h->smem_optin - 1024, &h->smm));
+    if (!h->smm.ok) return fail(-9, "k_smm does not fit on this device");
+    CUDA_TRY(dmalloc(&h->smm_scratch, (size_t)h->smm.grid * h->smm.scratch_doubles));
+  }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
   CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<96, 4, 96>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
@@ -368,7 +378,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaFree(h->d_tw); cudaFree(h->d_Dk);
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
   cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace); cudaFree(h->queues);
-  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status); cudaFree(h->cscratch);
+  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status); cudaFree(h->cscratch); cudaFree(h->smm_scratch);
   cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_Vf); cudaFree(h->g_Einv); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
@@ -451,6 +461,13 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
 }
 
 static void launch_tail(pirl_handle* h, KParams P, cudaStream_t st) {
+  if (h->cfg.algo == 1) {          // scattering-matrix form of the layer solve
+    StageTimer t(h, 11, st);
+    cudaError_t e = smm_launch(h->smm, P, h->smm_scratch, st);
+    if (e != cudaSuccess && h->sync_fail_stage < 0) { h->sync_fail_stage = 11; h->sync_err = e; }
+    h->launches += 1;
+    return;
+  }
   if (h->cluster && h->cplan.tail_ok && !h->no_rktail) {
     if (P.B > h->cplan.tail_clusters) P.queue = next_queue(h, st);
     StageTimer t(h, 10, st);
@@ -818,6 +835,7 @@ extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const
   if (B < 0) return fail(-2, "negative batch");
   if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
   CUDA_TRY(cudaSetDevice(h->cfg.device));
+  if (h->cfg.algo != 0) return fail(-4, "the adjoint gradient is implemented for algo = 0 (ETM) only");
   if (int rc = grad_prepare(h)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t mb = h->cfg.max_batch;

@@ -1,0 +1,330 @@
+// rcwa_smm.cuh -- scattering-matrix (algo = 'SMM') form of the layer solve: S_ref (*) S_layer (*) S_trn with Redheffer star
+// products (sm_100a).  The reference's alternative to the enhanced transmittance matrix method:
+//   scattering_1d_1/2/3   meent/on_numpy/scattering_method.py:12-73
+//   A_B_matrices(_half_space), S_layer, S_RT, RedhefferStar, homogeneous_1D   meent/on_numpy/smm_util.py:15-39, 42-67, 70-85,
+//                                                                             289-318, 136-182
+// It runs behind the same front kernels (modes W, eigenvalues lambda from rk_front / ck_front + k_ql + k_apply) in place of
+// the ETM tail, statement for statement in the operator sense: the same blocks A, B, S11..S22 are formed and combined with
+// the same products and inverses (general complex matrices, Gauss-Jordan with partial pivoting), in the REAL harmonic basis
+// {sqrt2 cos, sqrt2 sin, 1} -- a unitary change of basis that commutes with every diagonal medium matrix (they depend on
+// kx^2 only), so every block is the reference's block conjugated by that unitary and the efficiencies are identical.
+// One CTA per structure, blocks in an L2-resident per-CTA scratch.  This is the reference's slower variant (1.6x-2.9x its
+// TMM) and is not tuned: it exists so that algo = 'SMM' is a real operator, and as the stable form for
+// multilayer stacks.
+#pragma once
+#include "rcwa_common.cuh"
+
+constexpr int SMM_NT = 256;
+constexpr int SMM_NMAT = 20;          // complex ff x ff blocks of per-CTA scratch
+
+__host__ __device__ inline size_t smm_scratch_doubles(int ff) { return (size_t)SMM_NMAT * 2 * ff * ff + 2 * (size_t)ff * ff; }
+// shared: cre, cim [2N+1], per-harmonic complex diagonals vg, vr, vt, kzr, kzt, q, X [ff each], pattern bits, pivot slot
+__host__ __device__ inline int smm_smem_doubles(int ff, int N, int n_cells) {
+  return pirl_even(2 * (2 * N + 1)) + 2 * 7 * ff + pirl_even((n_cells + 7) / 8) + 8;
+}
+
+// C = A B  (n x n complex, row major); each thread owns 2 x 2 output blocks
+__device__ __forceinline__ void smm_gemm(cplx* __restrict__ C, const cplx* __restrict__ A, const cplx* __restrict__ B, int n, int tid) {
+  const int nb = (n + 1) / 2;
+  for (int blk = tid; blk < nb * nb; blk += SMM_NT) {
+    const int i0 = 2 * (blk / nb), j0 = 2 * (blk % nb);
+    const bool i1 = i0 + 1 < n, j1 = j0 + 1 < n;
+    cplx c00 = make_double2(0, 0), c01 = c00, c10 = c00, c11 = c00;
+    const cplx* a0 = A + (size_t)i0 * n;
+    const cplx* a1 = A + (size_t)(i1 ? i0 + 1 : i0) * n;
+    for (int k = 0; k < n; ++k) {
+      const cplx x0 = a0[k], x1 = a1[k];
+      const cplx y0 = B[(size_t)k * n + j0], y1 = B[(size_t)k * n + (j1 ? j0 + 1 : j0)];
+      c00 = cfma(x0, y0, c00); c01 = cfma(x0, y1, c01);
+      c10 = cfma(x1, y0, c10); c11 = cfma(x1, y1, c11);
+    }
+    C[(size_t)i0 * n + j0] = c00;
+    if (j1) C[(size_t)i0 * n + j0 + 1] = c01;
+    if (i1) { C[(size_t)(i0 + 1) * n + j0] = c10; if (j1) C[(size_t)(i0 + 1) * n + j0 + 1] = c11; }
+  }
+  __syncthreads();
+}
+
+// C = alpha A + beta B (+ gamma I)
+__device__ __forceinline__ void smm_axpby(cplx* C, double alpha, const cplx* A, double beta, const cplx* B, double gamma, int n, int tid) {
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {
+    cplx v = make_double2(0, 0);
+    if (A) { v.x += alpha * A[idx].x; v.y += alpha * A[idx].y; }
+    if (B) { v.x += beta * B[idx].x; v.y += beta * B[idx].y; }
+    if (gamma != 0.0 && idx / n == idx % n) v.x += gamma;
+    C[idx] = v;
+  }
+  __syncthreads();
+}
+
+// C = diag(dl) A diag(dr)  (either diagonal may be null)
+__device__ __forceinline__ void smm_scale(cplx* C, const cplx* dl, const cplx* A, const cplx* dr, int n, int tid) {
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {
+    const int i = idx / n, j = idx - i * n;
+    cplx v = A[idx];
+    if (dl) v = cmul(dl[i], v);
+    if (dr) v = cmul(v, dr[j]);
+    C[idx] = v;
+  }
+  __syncthreads();
+}
+
+// Ainv = A^-1 by Gauss-Jordan with partial pivoting on [A | I]; A is destroyed.  Returns (to every thread) whether a zero
+// pivot was met.  `slot`: one shared int.
+__device__ __forceinline__ bool smm_inverse(cplx* __restrict__ Ainv, cplx* __restrict__ A, int n, int tid, int* slot) {
+  const int lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = SMM_NT / 32;
+  bool singular = false;
+  for (int idx = tid; idx < n * n; idx += SMM_NT) Ainv[idx] = make_double2((idx / n == idx % n) ? 1.0 : 0.0, 0.0);
+  __syncthreads();
+  for (int k = 0; k < n; ++k) {
+    if (warp == 0) {
+      double best = -1.0; int bi = k;
+      for (int i = k + lane; i < n; i += 32) {
+        const cplx v = A[(size_t)i * n + k];
+        const double mg = fabs(v.x) + fabs(v.y);
+        if (mg > best) { best = mg; bi = i; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+      }
+      if (lane == 0) *slot = (best > 0.0) ? bi : -1;
+    }
+    __syncthreads();
+    const int pv = *slot;
+    if (pv < 0) { singular = true; __syncthreads(); continue; }
+    if (pv != k) {
+      for (int j = tid; j < 2 * n; j += SMM_NT) {
+        cplx* M = (j < n) ? A : Ainv;
+        const int jj = (j < n) ? j : j - n;
+        const cplx t0 = M[(size_t)k * n + jj]; M[(size_t)k * n + jj] = M[(size_t)pv * n + jj]; M[(size_t)pv * n + jj] = t0;
+      }
+    }
+    __syncthreads();
+    const cplx pinv = cinv(A[(size_t)k * n + k]);
+    __syncthreads();
+    for (int j = tid; j < 2 * n; j += SMM_NT) {        // scale the pivot row
+      cplx* M = (j < n) ? A : Ainv;
+      const int jj = (j < n) ? j : j - n;
+      M[(size_t)k * n + jj] = cmul(M[(size_t)k * n + jj], pinv);
+    }
+    __syncthreads();
+    for (int i = warp; i < n; i += NW) {               // eliminate column k from every other row
+      if (i == k) continue;
+      const cplx f = A[(size_t)i * n + k];
+      __syncwarp();
+      for (int j = lane; j < 2 * n; j += 32) {
+        cplx* M = (j < n) ? A : Ainv;
+        const int jj = (j < n) ? j : j - n;
+        if (j < n && jj <= k) { if (jj == k) M[(size_t)i * n + jj] = make_double2(0.0, 0.0); continue; }   // finished columns
+        M[(size_t)i * n + jj] = cfnma(f, M[(size_t)k * n + jj], M[(size_t)i * n + jj]);
+      }
+    }
+    __syncthreads();
+  }
+  return singular;
+}
+
+// RedhefferStar (smm_util.py:289-318): OUT = SA (*) SB.  Blocks are {S11, S12, S21, S22}; T0..T3 are temporaries.
+// Returns whether an inverse met a zero pivot.
+__device__ __forceinline__ bool smm_redheffer(cplx* const (&O)[4], cplx* const (&SA)[4], cplx* const (&SB)[4], cplx* T0, cplx* T1,
+                                              cplx* T2, cplx* T3, int n, int tid, int* slot) {
+  bool sing = false;
+  // D_i = inv(I - SB11 SA22)
+  smm_gemm(T0, SB[0], SA[3], n, tid);
+  smm_axpby(T0, -1.0, T0, 0.0, nullptr, 1.0, n, tid);
+  sing |= smm_inverse(T1, T0, n, tid, slot);                   // T1 = D_i
+  // F_i = inv(I - SA22 SB11)
+  smm_gemm(T0, SA[3], SB[0], n, tid);
+  smm_axpby(T0, -1.0, T0, 0.0, nullptr, 1.0, n, tid);
+  sing |= smm_inverse(T2, T0, n, tid, slot);                   // T2 = F_i
+  // S11 = SA11 + SA12 D_i SB11 SA21 ; S12 = SA12 D_i SB12
+  smm_gemm(T0, SA[1], T1, n, tid);                             // T0 = SA12 D_i
+  smm_gemm(O[1], T0, SB[1], n, tid);
+  smm_gemm(T3, T0, SB[0], n, tid);
+  smm_gemm(T0, T3, SA[2], n, tid);
+  smm_axpby(O[0], 1.0, SA[0], 1.0, T0, 0.0, n, tid);
+  // S21 = SB21 F_i SA21 ; S22 = SB22 + SB21 F_i SA22 SB12
+  smm_gemm(T0, SB[2], T2, n, tid);                             // T0 = SB21 F_i
+  smm_gemm(O[2], T0, SA[2], n, tid);
+  smm_gemm(T3, T0, SA[3], n, tid);
+  smm_gemm(T0, T3, SB[1], n, tid);
+  smm_axpby(O[3], 1.0, SB[3], 1.0, T0, 0.0, n, tid);
+  return sing;
+}
+
+// homogeneous_1D (smm_util.py:136-182) for one harmonic with normalised kx = kap: V = Q (-i Kz)^-1, Kz (times n^2 for TM when
+// `pol`); exact zeros are replaced by the reference's 1e-20 (1 + 1j) perturbation.
+__device__ __forceinline__ void smm_homogeneous(double kap, double n_index, bool pol, cplx* V, cplx* Kz) {
+  const double er = n_index * n_index, x = er - kap * kap;
+  cplx Q = make_double2(x, 0.0);
+  if (x == 0.0) Q = make_double2(1e-20, -1e-20);                       // conj(perturbation)
+  cplx kz = (x >= 0.0) ? make_double2(sqrt(x), 0.0) : make_double2(0.0, -sqrt(-x));   // conj(sqrt(x))
+  if (kz.x == 0.0 && kz.y == 0.0) kz = make_double2(1e-20, 1e-20);
+  if (pol) { kz.x *= er; kz.y *= er; }
+  const cplx ev = make_double2(kz.y, -kz.x);                           // -i Kz
+  *V = cmul(Q, cinv(ev));
+  *Kz = kz;
+}
+
+__global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ smm_scratch) {
+  extern __shared__ __align__(16) double sm[];
+  const int ff = P.ff, N = P.N, z = 2 * N, nc = P.n_cells, n = ff;
+  const int tid = threadIdx.x;
+  double* cre = sm;
+  double* cim = cre + (2 * N + 1);
+  cplx* vg = reinterpret_cast<cplx*>(sm + pirl_even(2 * (2 * N + 1)));
+  cplx* vr = vg + ff;
+  cplx* vt = vr + ff;
+  cplx* kzr = vt + ff;
+  cplx* kzt = kzr + ff;
+  cplx* qv = kzt + ff;
+  cplx* Xv = qv + ff;
+  uint8_t* su = reinterpret_cast<uint8_t*>(Xv + ff);
+  int* slot = reinterpret_cast<int*>(su + 8 * pirl_even((nc + 7) / 8));
+  cplx* base = reinterpret_cast<cplx*>(smm_scratch + (size_t)blockIdx.x * smm_scratch_doubles(ff));
+  const size_t m2 = (size_t)n * n;
+  cplx* M[SMM_NMAT];
+#pragma unroll
+  for (int i = 0; i < SMM_NMAT; ++i) M[i] = base + i * m2;
+  double* Amat = reinterpret_cast<double*>(base + SMM_NMAT * m2);      // [n][n] real: E^- convolution matrix in the real basis
+
+  for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
+    __syncthreads();
+    const double* pr = P.params + (size_t)b * P.pstride;
+    const double wl = pr[0], thick = pr[2], nr = pr[3];
+    const double sa = sin(pr[1] * (3.14159265358979323846 / 180.0));
+    const double k0d = 2.0 * 3.14159265358979323846 / wl * thick;
+    const double nI = P.n_inc, nII = P.n_exit, er = nr * nr, eg = P.eps_g;
+    for (int p = tid; p < nc; p += SMM_NT) su[p] = P.patterns[(size_t)b * nc + p] > 0;
+    __syncthreads();
+    // Fourier coefficients of the pattern (same closed form as the front kernels; convolution_matrix.py:101-114)
+    for (int k = tid; k <= 2 * N; k += SMM_NT) {
+      double sx = 0.0, sy = 0.0;
+      int idx = 0;
+      const int km = k % nc;
+      for (int p = 0; p < nc; ++p) {
+        if (su[p]) { const cplx w = __ldg(&P.tw[idx]); sx += w.x; sy += w.y; }
+        idx += km; if (idx >= nc) idx -= nc;
+      }
+      const cplx d = __ldg(&P.Dk[k]);
+      cre[k] = sx * d.x - sy * d.y;
+      cim[k] = sx * d.y + sy * d.x;
+    }
+    // per-harmonic media (scattering_1d_1, scattering_method.py:12-31), per-mode q and X (S_layer, smm_util.py:55)
+    const double* lam = P.lam + (size_t)b * ff;
+    for (int j = tid; j < ff; j += SMM_NT) {
+      const double kap = (j < z) ? ((j >> 1) + 1) * sa : 0.0;
+      cplx dummy;
+      smm_homogeneous(kap, 1.0, false, &vg[j], &dummy);               // gap medium, pol = None
+      smm_homogeneous(kap, nI, true, &vr[j], &kzr[j]);
+      smm_homogeneous(kap, nII, true, &vt[j], &kzt[j]);
+      const double l = lam[j];
+      if (l >= 0.0) { const double s = sqrt(l); qv[j] = make_double2(s, 0.0); Xv[j] = make_double2(exp(-k0d * s), 0.0); }
+      else { const double s = sqrt(-l); double sn, cn; sincos(k0d * s, &sn, &cn); qv[j] = make_double2(0.0, s); Xv[j] = make_double2(cn, -sn); }
+    }
+    __syncthreads();
+    // E^- in the real basis; W^-1 = W^T E^- (the modes are E^- -orthonormal: W^T E^- W = I)
+    {
+      const double da = 1.0 / er - 1.0 / eg, ia = 1.0 / eg;
+      for (int idx = tid; idx < n * n; idx += SMM_NT) {
+        const int i = idx / n, j = idx - i * n;
+        Amat[idx] = fma(da, basis_toeplitz(i, j, N, cre, cim), (i == j) ? ia : 0.0);
+      }
+    }
+    __syncthreads();
+    const double* Wg = P.Wbuf + (size_t)b * ff * ff;
+    cplx *A = M[0], *B = M[1], *Ai = M[2], *T0 = M[3], *T1 = M[4], *T2 = M[5], *T3 = M[6], *SL11 = M[7], *SL12 = M[8];
+    // A_B_matrices (smm_util.py:24-39) with Wg = I: A = W^-1 + V^-1 Vg, B = W^-1 - V^-1 Vg, V^-1 = Q^-1 W^T
+    for (int idx = tid; idx < n * n; idx += SMM_NT) {
+      const int m = idx / n, j = idx - m * n;
+      double winv = 0.0;
+      for (int i = 0; i < n; ++i) winv = fma(Wg[(size_t)i * n + m], Amat[(size_t)i * n + j], winv);
+      const cplx vi = cscale(cmul(cinv(qv[m]), vg[j]), Wg[(size_t)j * n + m]);
+      A[idx] = make_double2(winv + vi.x, vi.y);
+      B[idx] = make_double2(winv - vi.x, -vi.y);
+    }
+    __syncthreads();
+    bool sing = false;
+    // S_layer (smm_util.py:42-67)
+    smm_axpby(T0, 1.0, A, 0.0, nullptr, 0.0, n, tid);
+    sing |= smm_inverse(Ai, T0, n, tid, slot);                  // A_i
+    smm_gemm(T0, B, Ai, n, tid);
+    smm_scale(T1, Xv, T0, Xv, n, tid);                          // T1 = X B A_i X
+    smm_gemm(T2, T1, B, n, tid);
+    smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - X B A_i X B
+    sing |= smm_inverse(T3, T2, n, tid, slot);                  // term_i
+    smm_gemm(T0, T1, A, n, tid);
+    smm_axpby(T0, 1.0, T0, -1.0, B, 0.0, n, tid);
+    smm_gemm(SL11, T3, T0, n, tid);                             // S11 = S22
+    smm_gemm(T0, Ai, B, n, tid);
+    smm_gemm(T2, B, T0, n, tid);
+    smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - B A_i B
+    smm_scale(T0, Xv, T2, nullptr, n, tid);
+    smm_gemm(SL12, T3, T0, n, tid);                             // S12 = S21
+    // S_RT of the reflection region (A_B_matrices_half_space + S_RT, ref_mode = True): diagonal blocks, kept as matrices
+    cplx* R[4] = {M[9], M[10], M[11], M[12]};
+    for (int idx = tid; idx < n * n; idx += SMM_NT) {
+      const int i = idx / n, j = idx - i * n;
+      cplx s11 = make_double2(0, 0), s12 = s11, s21 = s11, s22 = s11;
+      if (i == j) {
+        const cplx rr = cmul(cinv(vg[i]), vr[i]);
+        const cplx a = make_double2(1.0 + rr.x, rr.y), bb = make_double2(1.0 - rr.x, -rr.y), ai = cinv(a);
+        s11 = cmul(make_double2(-bb.x, -bb.y), ai);
+        s12 = cscale(ai, 2.0);
+        s21 = cscale(csub(a, cmul(cmul(bb, ai), bb)), 0.5);
+        s22 = cmul(bb, ai);
+      }
+      R[0][idx] = s11; R[1][idx] = s12; R[2][idx] = s21; R[3][idx] = s22;
+    }
+    __syncthreads();
+    cplx* G[4] = {M[13], M[14], M[15], M[16]};
+    cplx* L[4] = {SL11, SL12, SL12, SL11};
+    sing |= smm_redheffer(G, R, L, T0, T1, T2, T3, n, tid, slot);       // Sg = S_ref (*) S_layer   (scattering_1d_2)
+    // transmission region (ref_mode = False: blocks swapped)
+    for (int idx = tid; idx < n * n; idx += SMM_NT) {
+      const int i = idx / n, j = idx - i * n;
+      cplx s11 = make_double2(0, 0), s12 = s11, s21 = s11, s22 = s11;
+      if (i == j) {
+        const cplx rr = cmul(cinv(vg[i]), vt[i]);
+        const cplx a = make_double2(1.0 + rr.x, rr.y), bb = make_double2(1.0 - rr.x, -rr.y), ai = cinv(a);
+        s11 = cmul(make_double2(-bb.x, -bb.y), ai);
+        s12 = cscale(ai, 2.0);
+        s21 = cscale(csub(a, cmul(cmul(bb, ai), bb)), 0.5);
+        s22 = cmul(bb, ai);
+      }
+      R[0][idx] = s22; R[1][idx] = s21; R[2][idx] = s12; R[3][idx] = s11;
+    }
+    __syncthreads();
+    cplx* F[4] = {M[0], M[1], M[2], M[17]};
+    sing |= smm_redheffer(F, G, R, T0, T1, T2, T3, n, tid, slot);       // Sg = Sg (*) S_trn        (scattering_1d_3)
+    // fields of the incident zeroth order (c_inc = delta: W_r = I) and efficiencies of orders -1, 0, +1
+    if (tid == 0) {
+      const cplx Rc = F[0][(size_t)0 * n + z], Rs = F[0][(size_t)1 * n + z], R0 = F[0][(size_t)z * n + z];
+      const cplx Tc = F[2][(size_t)0 * n + z], Ts = F[2][(size_t)1 * n + z], T0c = F[2][(size_t)z * n + z];
+      const double is2 = 0.7071067811865476;
+      const cplx Tm = make_double2((Tc.x - Ts.y) * is2, (Tc.y + Ts.x) * is2);
+      const cplx Tp = make_double2((Tc.x + Ts.y) * is2, (Tc.y - Ts.x) * is2);
+      const cplx Rm = make_double2((Rc.x - Rs.y) * is2, (Rc.y + Rs.x) * is2);
+      const cplx Rp = make_double2((Rc.x + Rs.y) * is2, (Rc.y - Rs.x) * is2);
+      // de_ri = Re(Kzr) |r|^2 / Re(k_inc_z) / n_I^2 ; de_ti = Re(Kzt) |t|^2 / Re(k_inc_z) n_I^2 / n_II^4   (scattering_method.py:66-69)
+      const double kinc = nI;
+      double der[3], det[3];
+      der[0] = kzr[0].x * (Rm.x * Rm.x + Rm.y * Rm.y) / kinc / (nI * nI);
+      der[1] = kzr[z].x * (R0.x * R0.x + R0.y * R0.y) / kinc / (nI * nI);
+      der[2] = kzr[0].x * (Rp.x * Rp.x + Rp.y * Rp.y) / kinc / (nI * nI);
+      det[0] = kzt[0].x * (Tm.x * Tm.x + Tm.y * Tm.y) / kinc * (nI * nI) / (nII * nII * nII * nII);
+      det[1] = kzt[z].x * (T0c.x * T0c.x + T0c.y * T0c.y) / kinc * (nI * nI) / (nII * nII * nII * nII);
+      det[2] = kzt[0].x * (Tp.x * Tp.x + Tp.y * Tp.y) / kinc * (nI * nI) / (nII * nII * nII * nII);
+      int st = P.wstatus[b];
+      if (sing || !isfinite(det[0]) || !isfinite(det[1]) || !isfinite(der[1])) st |= PIRL_ST_NONFINITE_;
+      P.eff[b] = det[0];
+      if (P.de_r3) { P.de_r3[3 * b] = der[0]; P.de_r3[3 * b + 1] = der[1]; P.de_r3[3 * b + 2] = der[2]; }
+      if (P.de_t3) { P.de_t3[3 * b] = det[0]; P.de_t3[3 * b + 1] = det[1]; P.de_t3[3 * b + 2] = det[2]; }
+      if (P.status) P.status[b] = st;
+    }
+  }
+}

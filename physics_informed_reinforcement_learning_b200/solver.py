@@ -31,7 +31,7 @@ class RCWABatch:
     """Batched 1D TM RCWA of binary deflectors on one B200 (replaces JLABCode + RCWALight for B structures)."""
 
     def __init__(self, n_cells=256, order=40, n_I=1.45, n_II=1.0, n_groove=1.0, theta=0.0, pol=1,
-                 max_batch=4096, device=None):
+                 max_batch=4096, device=None, algo='TMM'):
         torch = _torch()
         if not torch.cuda.is_available():
             raise RuntimeError("RCWABatch needs a CUDA device (B200); there is no CPU fallback")
@@ -41,9 +41,12 @@ class RCWABatch:
         self.device = torch.device("cuda", device if isinstance(device, int) else torch.device(device).index or 0)
         self.n_cells, self.order, self.ff = int(n_cells), int(order), 2 * int(order) + 1
         self.n_I, self.n_II, self.n_groove = float(n_I), float(n_II), float(n_groove)
+        if algo not in ('TMM', 'SMM', 0, 1):
+            raise ValueError(algo)                       # rcwa.py:31-32
+        self.algo = 1 if algo in ('SMM', 1) else 0       # 'TMM': enhanced transmittance matrices; 'SMM': Redheffer star products
         cfg = _lib.PirlCfg(n_cells=self.n_cells, order=self.order, n_inc=self.n_I, n_exit=self.n_II,
                            n_groove=self.n_groove, theta_deg=float(theta), pol=int(pol), max_batch=int(max_batch),
-                           device=self.device.index, reserved=0)
+                           device=self.device.index, algo=self.algo, precision=0)
         h = C.c_void_p()
         _lib.check(self.lib.pirl_rcwa_create(C.byref(cfg), C.byref(h)))
         self._h = h
@@ -232,15 +235,15 @@ _backends = {}
 _backends_lock = threading.Lock()
 
 
-def shared_backend(n_cells, order, n_I=1.45, n_II=1.0, n_groove=1.0, max_batch=4096, device=None) -> RCWABatch:
+def shared_backend(n_cells, order, n_I=1.45, n_II=1.0, n_groove=1.0, max_batch=4096, device=None, algo='TMM') -> RCWABatch:
     """One cached handle per configuration (the reference builds a solver object per call; here the
     workspaces are allocated once)."""
     torch = _torch()
     dev = torch.cuda.current_device() if device is None else device
-    key = (int(n_cells), int(order), float(n_I), float(n_II), float(n_groove), int(max_batch), dev)
+    key = (int(n_cells), int(order), float(n_I), float(n_II), float(n_groove), int(max_batch), dev, algo)
     with _backends_lock:
         if key not in _backends:
-            _backends[key] = RCWABatch(n_cells, order, n_I, n_II, n_groove, max_batch=max_batch, device=dev)
+            _backends[key] = RCWABatch(n_cells, order, n_I, n_II, n_groove, max_batch=max_batch, device=dev, algo=algo)
         return _backends[key]
 
 
@@ -261,6 +264,7 @@ class JLABCode:
             raise ValueError(algo)
         if theta != 0 or phi != 0:
             raise ValueError("only normal incidence is on the accelerated path")
+        self.algo = algo            # 'SMM' runs the scattering-matrix kernel (k_smm), 'TMM' the transmittance-matrix tails
         self.n_I, self.n_II = n_I, n_II
         self.fourier_order = fourier_order
         self.period = np.atleast_1d(np.asarray(period, dtype=np.float64))
@@ -282,7 +286,7 @@ class JLABCode:
         # period = wl / sin(angle)  ->  the kernels take the deflection angle
         ratio = wl / float(self.period[0])
         angle = np.degrees(np.arcsin(ratio))
-        be = shared_backend(struct.size, self.fourier_order, self.n_I, self.n_II, float(n_groove), max_batch=64)
+        be = shared_backend(struct.size, self.fourier_order, self.n_I, self.n_II, float(n_groove), max_batch=64, algo=self.algo)
         eff, r3, t3, st = be.evaluate_host(struct[None, :], wl, angle, float(self.thickness[0]), float(n_ridge),
                                            return_orders=True)
         if st[0] & (ST_EIG_NOT_CONVERGED | ST_NOT_POSDEF):

@@ -464,3 +464,41 @@ def test_cluster_small_variant_matches_register_tile_kernels(pkg, torch_mod):
     assert int(st.abs().sum()) == 0 and times["ck_front"][1] == 1 and times["ck_tail"][1] == 1
     assert float((e - e_ref).abs().max()) <= 1e-9 and float((t - t_ref).abs().max()) <= 1e-9 and float((r - r_ref).abs().max()) <= 1e-9
     ref.close(); ck.close()
+
+
+def test_smm_scattering_matrix_operator(golden_dir, pkg, torch_mod):
+    """algo = 'SMM' (scattering_method.py:12-73, smm_util.py): k_smm builds S_ref, S_layer, S_trn and combines them with
+    Redheffer star products.  Against the reference's own SMM result (golden G1_rand256_N40_SMM), against the oracle on
+    random / blocky patterns at three orders (ETM and SMM agree to ~1e-13 in the reference), against
+    the ETM kernels of this library, and through the JLABCode drop-in."""
+    torch = torch_mod
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(21)
+    for n_cells, order, count in ((256, 40, 24), (96, 12, 16), (256, 64, 6)):
+        pats = (rng.integers(0, 2, (count, n_cells)) * 2 - 1).astype(np.int8)
+        pats[::2] = np.repeat(rng.integers(0, 2, (count // 2, n_cells // 16)) * 2 - 1, 16, axis=1)
+        smm = pkg.RCWABatch(n_cells, order, max_batch=16, device=0, algo='SMM')
+        etm = pkg.RCWABatch(n_cells, order, max_batch=16, device=0)
+        smm.set_stage_timing(True)
+        e_s, r_s, t_s, st = smm.evaluate_host(pats, 1100.0, 60.0, 325.0, return_orders=True)
+        times = smm.stage_times()
+        e_e, r_e, t_e, _ = etm.evaluate_host(pats, 1100.0, 60.0, 325.0, return_orders=True)
+        assert not st.any() and times["k_smm"][1] >= 1 and times["k_tail"][1] == 0 and times["rk_tail"][1] == 0
+        assert np.abs(e_s - e_e).max() <= 1e-9 and np.abs(r_s - r_e).max() <= 1e-9 and np.abs(t_s - t_e).max() <= 1e-9
+        for i in range(0, count, 3):
+            r = O.evaluate(pats[i].astype(np.float64), 1100.0, 60.0, order, 325.0)
+            assert abs(e_s[i] - r.eff) <= 1e-9
+            assert np.abs(t_s[i] - r.de_ti[order - 1:order + 2]).max() <= 1e-9 and np.abs(r_s[i] - r.de_ri[order - 1:order + 2]).max() <= 1e-9
+        with pytest.raises(ValueError):
+            smm.evaluate_grad(torch.from_numpy(pats).cuda())            # the adjoint sweep exists for the ETM form only
+        smm.close(); etm.close()
+    # the reference's own SMM run of G1 (fixture written by oracle/make_golden.py from the unmodified reference, algo='SMM')
+    g, names = _named(golden_dir)
+    assert "G1_rand256_N40_SMM" in names
+    pat = g["G1_rand256_N40_SMM/pattern"]
+    assert abs(float(g["G1_rand256_N40_SMM/ref_eff"]) - 0.0004665720258772289) <= 1e-15
+    code = pkg.JLABCode(n_I=1.45, n_II=1., theta=0, phi=0, fourier_order=40, period=[abs(1100 / np.sin(60 / 180 * np.pi))],
+                        wls=np.array([1100.]), pol=1, ucell=pat[None, None, :], thickness=[325], algo='SMM')
+    eff, refl, tran = code.reproduce_acs_cell('p_si__real', 1)
+    assert abs(eff - float(g["G1_rand256_N40_SMM/ref_eff"])) <= 1e-12
+    assert np.abs(tran - g["G1_rand256_N40_SMM/ref_tran_cut"]).max() <= 1e-12 and np.abs(refl - g["G1_rand256_N40_SMM/ref_refl_cut"]).max() <= 1e-12

@@ -92,7 +92,7 @@ def test_library_exports_every_declared_symbol():
     lib = ctypes.CDLL(LIB_PATH)
     for name in declared:
         assert hasattr(lib, name), name
-    assert _lib.load().pirl_abi_version() == 1
+    assert _lib.load().pirl_abi_version() == 2
 
 
 def test_create_fails_loudly_without_gpu():
@@ -101,7 +101,7 @@ def test_create_fails_loudly_without_gpu():
         pytest.skip("GPU present")
     lib = _lib.load()
     cfg = _lib.PirlCfg(n_cells=256, order=40, n_inc=1.45, n_exit=1.0, n_groove=1.0, theta_deg=0.0, pol=1,
-                       max_batch=8, device=0, reserved=0)
+                       max_batch=8, device=0)
     h = ctypes.c_void_p()
     rc = lib.pirl_rcwa_create(ctypes.byref(cfg), ctypes.byref(h))
     assert rc != 0 and b"CPU fallback" in lib.pirl_last_error()
@@ -113,9 +113,10 @@ def test_create_fails_loudly_without_gpu():
 def test_argument_errors_reported_before_touching_the_device():
     lib = _lib.load()
     h = ctypes.c_void_p()
-    for kw in (dict(pol=0), dict(theta_deg=10.0), dict(order=0), dict(order=200), dict(max_batch=0)):
+    for kw in (dict(pol=0), dict(theta_deg=10.0), dict(order=0), dict(order=200), dict(max_batch=0), dict(algo=2),
+               dict(precision=1)):
         base = dict(n_cells=256, order=40, n_inc=1.45, n_exit=1.0, n_groove=1.0, theta_deg=0.0, pol=1, max_batch=8,
-                    device=0, reserved=0)
+                    device=0)
         base.update(kw)
         cfg = _lib.PirlCfg(**base)
         assert lib.pirl_rcwa_create(ctypes.byref(cfg), ctypes.byref(h)) < 0, kw
