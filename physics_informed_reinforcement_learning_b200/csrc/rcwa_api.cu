@@ -60,7 +60,7 @@ struct pirl_handle {
   int front_grid, front_mats; size_t front_smem;
   int tri_grid, tri_mats; size_t tri_smem;
   int tail_grid, tail_mats; size_t tail_smem;
-  int apply_rows, apply_k; size_t apply_smem;
+  int apply_rows, apply_k; size_t apply_smem; int apply_variant = 0;   // variant > 0: experiment instances for ff > 96 (PIRL_APPLY)
   size_t ql_smem;
   unsigned long long* phase_clk = nullptr;   // [32] device counters (PIRL_PHASE_CLOCKS=1)
   unsigned long long* trace = nullptr;       // CTA trace records (PIRL_TRACE=1)
@@ -269,6 +269,17 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     else if (h->apply_rows == 96) CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4, 96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
     else if (h->apply_rows == 64) CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
     else CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)abudget));
+    // large orders (96 < ff <= 208): more sweeps per systolic pass and smaller row blocks -> more independent rotation chains
+    // per SM (the 64-row / 2-sweep variant runs ONE 64-thread CTA per SM at ff = 201: profiles/r02k_ncu_full_c5_*.csv)
+    if (ff > 96 && ff <= 208) {
+      int v = 2;      // measured at order 100, batch 512 (profiles/r02l_apply_variants.txt): 0: 8.25 ms, 1: 7.32, 2: 6.46, 3: 6.95
+      if (const char* e = getenv("PIRL_APPLY")) v = atoi(e);
+      h->apply_variant = v;
+      if (v == 1) { h->apply_rows = 32; h->apply_k = 4; h->apply_smem = apply_bytes(32, 4); CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 4, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<32, 4, 208>)); }
+      else if (v == 2) { h->apply_rows = 64; h->apply_k = 4; h->apply_smem = apply_bytes(64, 4); CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 4, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<64, 4, 208>)); }
+      else if (v == 3) { h->apply_rows = 32; h->apply_k = 2; h->apply_smem = apply_bytes(32, 2); CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<32, 2, 208>)); }
+      else h->apply_variant = 0;
+    }
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
   }
@@ -453,7 +464,10 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
     StageTimer t(h, 3, st);
     dim3 g(P.B, (h->ff + h->apply_rows - 1) / h->apply_rows);
     // (the third template argument sizes the static rotation buffers: ff <= 81 keeps three CTAs per SM at the headline size)
-    if (h->apply_rows == 96 && h->ff <= 81) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
+    if (h->apply_variant == 1) k_apply<32, 4, 208><<<g, 32, h->apply_smem, st>>>(P);
+    else if (h->apply_variant == 2) k_apply<64, 4, 208><<<g, 64, h->apply_smem, st>>>(P);
+    else if (h->apply_variant == 3) k_apply<32, 2, 208><<<g, 32, h->apply_smem, st>>>(P);
+    else if (h->apply_rows == 96 && h->ff <= 81) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 96) k_apply<96, 4, 96><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 64) k_apply<64, 2, 256><<<g, 64, h->apply_smem, st>>>(P);
     else k_apply<32, 2, 256><<<g, 32, h->apply_smem, st>>>(P);
