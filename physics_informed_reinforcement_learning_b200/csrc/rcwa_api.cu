@@ -78,6 +78,7 @@ struct pirl_handle {
   cudaStream_t own_stream = nullptr;
   // adjoint gradient (allocated on the first pirl_rcwa_eval_grad)
   double *g_lamb = nullptr, *g_Lf = nullptr, *g_Rf = nullptr, *g_Vf = nullptr, *g_Einv = nullptr, *g_scr_tail = nullptr, *g_scr_eig = nullptr;
+  int g_eig_mma = 0;   // PIRL_GEIG_DMMA: GEMMs of g_eigback on mma.sync.m8n8k4.f64 tiles
   int g_tail_grid = 0, g_tail_mats = 0, g_eig_grid = 0, g_eig_mats = 0; bool g_tail_regtile = false; int g_tail_packed = 0, g_tail_lu_k0 = 0;
   size_t g_tail_smem = 0, g_eig_smem = 0, g_tail_stride = 0, g_eig_stride = 0;
   double* hd_grad = nullptr; int64_t hd_grad_cap = 0;
@@ -559,6 +560,7 @@ static void launch_gtail(pirl_handle* h, const KParams& P, GParams G, cudaStream
 static void launch_geig(pirl_handle* h, const KParams& P, GParams G, cudaStream_t st) {
   StageTimer t(h, 8, st);
   G.gscratch = h->g_scr_eig; G.gstride = h->g_eig_stride; G.smem_mats = h->g_eig_mats; G.packed = 0; G.lu_k0 = 0;
+  G.use_mma = h->g_eig_mma;
   if (h->g_eig_mats >= 4) g_eigback<GEIG_NT, true><<<std::min(P.B, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
   else g_eigback<GEIG_NT, false><<<std::min(P.B, h->g_eig_grid), GEIG_NT, h->g_eig_smem, st>>>(P, G);
   h->launches += 1;
@@ -830,6 +832,9 @@ static int grad_prepare(pirl_handle* h) {
   else
     rc = plan_grad_kernel(h, g_eigback<GEIG_NT, false>, GEIG_NT, evec, rmat, 4, &h->g_eig_mats, &h->g_eig_smem, &h->g_eig_grid);
   if (rc) return rc;
+  // measured (profiles/r02m_dmma_trial.txt): g_eigback 4.79 -> 3.85 ms per 4096 at order 40, 7.72 -> 6.74 ms per 2048 at order 60
+  h->g_eig_mma = 1;
+  if (const char* e = getenv("PIRL_GEIG_DMMA")) h->g_eig_mma = atoi(e);
   h->g_tail_stride = grad_tail_scratch_doubles(ff, h->ld);
   h->g_eig_stride = grad_eig_scratch_doubles(ff, h->ld);
   CUDA_TRY(dmalloc(&h->g_scr_tail, (size_t)h->g_tail_grid * h->g_tail_stride));
@@ -860,6 +865,7 @@ extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const
                              nullptr, nullptr, status ? status + off : nullptr);
     P.Einv = h->g_Einv;
     GParams G;
+    memset(&G, 0, sizeof(G));
     G.lamb = h->g_lamb; G.Lf = h->g_Lf; G.Rf = h->g_Rf; G.Vf = h->g_Vf; G.grad = grad + off * h->cfg.n_cells;
     if (int rc = launch_chunk(h, P, Bc, st, &G)) return rc;
   }

@@ -30,6 +30,7 @@ struct GParams {
   int smem_mats;       // matrices held in shared memory (kernel specific)
   int packed;          // g_tail, shared-memory variant: G_II is inverted as a packed lower triangle in shared memory
   int lu_k0;           // ... and the trailing block [lu_k0, ff)^2 of S is factorised in shared memory (ff: never)
+  int use_mma;         // g_eigback: the six real GEMMs on FP64 tensor tiles (mma.sync.m8n8k4.f64) instead of register-tiled DFMA
 };
 
 __host__ __device__ inline int grad_tail_vec_doubles(int ff) { return tail_vec_doubles(ff) + pirl_even(ff / 2 + 2) + pirl_even(ff); }
@@ -1046,11 +1047,71 @@ __device__ __forceinline__ void cta_gemm_rt(double* __restrict__ C, const double
       }
     }
 }
+// The same GEMM on the FP64 tensor path: mma.sync.aligned.m8n8k4.f64 (legacy warp-level DMMA; tcgen05 has no FP64 kind).
+// 8 warps; C is cut in 8 x 8 tiles, a warp owns blocks of 3 x 3 tiles (ff = 81: 11 x 11 tiles -> 16 blocks, two per warp)
+// and walks k in steps of 4: three A fragments + three B fragments (one double per lane each) feed nine DMMAs.
+// Fragment layout (PTX ISA, m8n8k4 .f64): A[row = lane / 4][k = lane % 4], B[k = lane % 4][col = lane / 4],
+// C[row = lane / 4][col = 2 (lane % 4) + {0, 1}].  Out-of-range rows / columns / k read as zero.
+template <bool TRANS_B>
+__device__ __forceinline__ void cta_gemm_mma(double* __restrict__ C, const double* __restrict__ A, const double* __restrict__ B,
+                                             int ff, int ld) {
+  constexpr int TB = 3;                              // tiles per block side
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int nt = (ff + 7) / 8, nb = (nt + TB - 1) / TB;
+  for (int blk = warp; blk < nb * nb; blk += nwarps) {
+    const int bi = blk / nb, bj = blk - bi * nb;
+    double acc[TB][TB][2];
+    int arow[TB], bcol[TB];
+    bool aok[TB], bok[TB];
+#pragma unroll
+    for (int r = 0; r < TB; ++r) {
+      const int i = (bi * TB + r) * 8 + g, j = (bj * TB + r) * 8 + g;
+      aok[r] = i < ff; bok[r] = j < ff;
+      arow[r] = min(i, ff - 1) * ld;
+      bcol[r] = TRANS_B ? min(j, ff - 1) * ld : min(j, ff - 1);
+#pragma unroll
+      for (int c = 0; c < TB; ++c) { acc[r][c][0] = 0.0; acc[r][c][1] = 0.0; }
+    }
+    for (int k0 = 0; k0 < ff; k0 += 4) {
+      const int k = k0 + t4;
+      const bool kok = k < ff;
+      const int kc = min(k, ff - 1);
+      double a[TB], b[TB];
+#pragma unroll
+      for (int r = 0; r < TB; ++r) {
+        const double av = A[arow[r] + kc];
+        const double bv = TRANS_B ? B[bcol[r] + kc] : B[kc * ld + bcol[r]];
+        a[r] = (aok[r] && kok) ? av : 0.0;
+        b[r] = (bok[r] && kok) ? bv : 0.0;
+      }
+#pragma unroll
+      for (int r = 0; r < TB; ++r)
+#pragma unroll
+        for (int c = 0; c < TB; ++c)
+          asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                       : "+d"(acc[r][c][0]), "+d"(acc[r][c][1])
+                       : "d"(a[r]), "d"(b[c]));
+    }
+#pragma unroll
+    for (int r = 0; r < TB; ++r) {
+      const int i = (bi * TB + r) * 8 + g;
+#pragma unroll
+      for (int c = 0; c < TB; ++c) {
+        const int j = (bj * TB + c) * 8 + 2 * t4;
+        if (i < ff && j < ff) C[i * ld + j] = acc[r][c][0];
+        if (i < ff && j + 1 < ff) C[i * ld + j + 1] = acc[r][c][1];
+      }
+    }
+  }
+}
+
 // register tile 6 x 6 (96 x 96 per pass) up to ff = 96, 8 x 8 (128 x 128 per pass) beyond: ff = 121 is one pass instead of four
 template <bool TRANS_B>
 __device__ __forceinline__ void cta_gemm(double* __restrict__ C, const double* __restrict__ A, const double* __restrict__ B,
-                                         int ff, int ld) {
-  if (ff <= 96) cta_gemm_rt<TRANS_B, 6>(C, A, B, ff, ld);
+                                         int ff, int ld, int use_mma = 0) {
+  if (use_mma) cta_gemm_mma<TRANS_B>(C, A, B, ff, ld);
+  else if (ff <= 96) cta_gemm_rt<TRANS_B, 6>(C, A, B, ff, ld);
   else cta_gemm_rt<TRANS_B, 8>(C, A, B, ff, ld);
 }
 
@@ -1233,13 +1294,13 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     }
     __syncthreads();
     RK_PHASE(24);
-    cta_gemm<false>(M3, M0, M1, ff, ld);                 // W G_B
+    cta_gemm<false>(M3, M0, M1, ff, ld, G.use_mma);                 // W G_B
     __syncthreads();
-    cta_gemm<true>(M1, M3, M0, ff, ld);                  // B-bar = W G_B W^T
+    cta_gemm<true>(M1, M3, M0, ff, ld, G.use_mma);                  // B-bar = W G_B W^T
     __syncthreads();
-    cta_gemm<false>(M3, M0, M2, ff, ld);                 // W G_A
+    cta_gemm<false>(M3, M0, M2, ff, ld, G.use_mma);                 // W G_A
     __syncthreads();
-    cta_gemm<true>(M2, M3, M0, ff, ld);                  // A-bar = W G_A W^T
+    cta_gemm<true>(M2, M3, M0, ff, ld, G.use_mma);                  // A-bar = W G_A W^T
     __syncthreads();
     RK_PHASE(25);
     for (int i = warp; i < ff; i += NW)
@@ -1264,9 +1325,9 @@ __global__ void __launch_bounds__(NT) g_eigback(KParams P, GParams G) {
     }
     for (int t = tid; t < ff; t += NT) { M3[z * ld + t] = 0.0; M3[t * ld + z] = 0.0; }
     __syncthreads();
-    cta_gemm<false>(M2, M0, M3, ff, ld);
+    cta_gemm<false>(M2, M0, M3, ff, ld, G.use_mma);
     __syncthreads();
-    cta_gemm<false>(M1, M2, M0, ff, ld);                 // -E-bar = E^-1 (E^-1)-bar E^-1
+    cta_gemm<false>(M1, M2, M0, ff, ld, G.use_mma);                 // -E-bar = E^-1 (E^-1)-bar E^-1
     __syncthreads();
     RK_PHASE(28);
     for (int i = warp; i < ff; i += NW)
