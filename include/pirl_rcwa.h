@@ -41,7 +41,8 @@ typedef struct pirl_cfg {
   double n_exit;       /* n_II = 1.0                                                      */
   double n_groove;     /* 1.0                                                             */
   double theta_deg;    /* incidence angle; only 0 is supported (as DeflectorGym uses)     */
-  int32_t pol;         /* 1 = TM (the only polarisation on this path)                     */
+  int32_t pol;         /* 1 = TM (what DeflectorGym evaluates; register-tile / cluster kernels), 0 = TE
+                          (_base.py:142-148: generic front kernels + the S-matrix layer solve)    */
   int32_t max_batch;   /* structures processed per internal chunk (workspace sizing)      */
   int32_t device;      /* CUDA device ordinal                                             */
   int32_t algo;        /* 0 = ETM / 'TMM' (transfer_method.py:4-75, the default of the reference),
@@ -92,6 +93,24 @@ int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const double* pa
 /* Same with HOST buffers (H2D, eval + gradient, D2H, synchronous). */
 int pirl_rcwa_eval_grad_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
                              int64_t B, double* eff, double* grad, int32_t* status);
+
+/* Layer stacks: the reference's layer loop (_base.py:141, JLABCode with ucell of shape (L, 1, n_cells), JLAB/solver.py:16-38).
+ *   patterns   device, int8 [B][n_layers][n_cells], layers in the reference's LIST order
+ *   params     device, double [B][4] or [1][4]: {wavelength_nm, deflection_angle_deg, (ignored), n_ridge}
+ *   thickness  device, double [B][n_layers] or [1][n_layers] (thickness_stride = n_layers or 0)
+ * Every (structure, layer) pair is one eigenproblem of the front kernels (n_layers <= max_batch); the layers of a structure
+ * are combined with Redheffer star products (smm_util.py:289-318).  cfg.algo keeps the reference's layer ORDER per
+ * algorithm: 0 ('TMM') = list order from the incidence side; 1 ('SMM') = the reversed list -- the reference walks the list
+ * backwards for both algorithms, which for its S-matrix form appends the layers in reversed order (its 'SMM' result of a
+ * list equals its 'TMM' result of the reversed list; verified against the unmodified reference, tests/golden/
+ * rcwa_stack_golden.npz).  Outputs as pirl_rcwa_eval. */
+int pirl_rcwa_eval_stack(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                         const double* thickness, int32_t thickness_stride, int32_t n_layers, int64_t B, double* eff,
+                         double* de_r3, double* de_t3, int32_t* status, void* stream);
+/* Same with HOST buffers (H2D, solve, D2H, synchronous). */
+int pirl_rcwa_eval_stack_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                              const double* thickness, int32_t thickness_stride, int32_t n_layers, int64_t B, double* eff,
+                              double* de_r3, double* de_t3, int32_t* status);
 
 /* DeflectorBase.flip for B envs (base.py:37-42): patterns[b][a] = -patterns[b][a] iff 0 <= a <= n_cells-1. */
 int pirl_env_flip(int8_t* patterns, const int64_t* actions, int64_t B, int32_t n_cells, void* stream);

@@ -204,3 +204,143 @@ def fd_gradient(struct, idx, wavelength=1100.0, angle=60.0, order=40, thickness=
         out[j] = (efficiency(sp, wavelength, angle, order, thickness)
                   - efficiency(sm, wavelength, angle, order, thickness)) / (2 * h)
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# General 1D stack: both polarisations, both algorithms, any number of layers (normal or oblique incidence in the plane).
+# Restates _BaseRCWA.solve_1d (_base.py:119-180), transfer_1d_1/2/3 (transfer_method.py:4-75) and scattering_1d_1/2/3 with
+# their helpers (scattering_method.py:12-73; smm_util.py:15-85, 136-182, 289-318).  Pinned by the multilayer / TE fixtures in
+# tests/golden/rcwa_stack_golden.npz, written by oracle/make_stack_golden.py from the unmodified reference.
+# NB the reference walks the layers in REVERSED list order for BOTH algorithms (_base.py:141).  For 'TMM' that builds the
+# stack from the exit side up (list order = incidence side first); for 'SMM' the star products then append the layers to the
+# reflection-side matrix in reversed list order, i.e. the SMM result of a list equals the TMM result of the reversed list.
+# The restatement keeps that behaviour.
+# ---------------------------------------------------------------------------------------------------------------------
+def _homogeneous_1d(kx_norm, n_index, pol):
+    """smm_util.py:136-182 on the diagonal: returns (V, Kz) as vectors (W = I)."""
+    e_r = n_index ** 2
+    pert = 1e-20 * (1 + 1j)
+    Q = (e_r - kx_norm ** 2).astype(complex)
+    Q[Q == 0] = np.conj(pert)
+    Kz = np.conj(np.sqrt((e_r - kx_norm ** 2).astype(complex)))
+    Kz[Kz == 0] = pert
+    if pol:
+        Kz = Kz * n_index ** 2
+    V = Q / (-1j * Kz)
+    return V, Kz
+
+
+def _s_rt(A, B, ref_mode):
+    """smm_util.py:70-85."""
+    A_i = np.linalg.inv(A)
+    S11, S12, S21, S22 = -A_i @ B, 2 * A_i, 0.5 * (A - B @ A_i @ B), B @ A_i
+    if ref_mode:
+        return dict(S11=S11, S22=S22, S12=S12, S21=S21)
+    return dict(S11=S22, S22=S11, S12=S21, S21=S12)
+
+
+def _redheffer(SA, SB):
+    """smm_util.py:289-318."""
+    n = len(SA['S11'])
+    I = np.eye(n)
+    D_i = np.linalg.inv(I - SB['S11'] @ SA['S22'])
+    F_i = np.linalg.inv(I - SA['S22'] @ SB['S11'])
+    return dict(S11=SA['S11'] + SA['S12'] @ D_i @ SB['S11'] @ SA['S21'], S12=SA['S12'] @ D_i @ SB['S12'],
+                S21=SB['S21'] @ F_i @ SA['S21'], S22=SB['S22'] + SB['S21'] @ F_i @ SA['S22'] @ SB['S12'])
+
+
+def solve_stack(e_convs, oe_convs, thicknesses, wavelength, period, order, pol=1, algo='TMM',
+                n_inc=N_INCIDENT, n_exit=N_EXIT, theta=0.0):
+    """de_ri, de_ti of a stack of grating layers (lists in the reference's list order)."""
+    ff = 2 * order + 1
+    m = np.arange(-order, order + 1)
+    delta = np.zeros(ff)
+    delta[order] = 1.0
+    k0 = 2.0 * np.pi / wavelength
+    I = np.eye(ff)
+    if algo == 'TMM':                                       # transfer_1d_1
+        kx = k0 * (n_inc * np.sin(theta) - m * (wavelength / period)).astype(complex)
+        kz_inc = np.conj((k0 ** 2 * n_inc ** 2 - kx ** 2) ** 0.5)
+        kz_exit = np.conj((k0 ** 2 * n_exit ** 2 - kx ** 2) ** 0.5)
+        Kx = np.diag(kx / k0)
+        f = np.eye(ff)
+        if pol == 0:
+            YZ_I = np.diag(kz_inc / k0); g = 1j * np.diag(kz_exit / k0); inc = 1j * n_inc * np.cos(theta) * delta
+        else:
+            YZ_I = np.diag(kz_inc / (k0 * n_inc ** 2)); g = 1j * np.diag(kz_exit / (k0 * n_exit ** 2))
+            inc = 1j * delta * np.cos(theta) / n_inc
+        T = np.eye(ff)
+    elif algo == 'SMM':                                     # scattering_1d_1
+        kxn = (n_inc * np.sin(theta) - m * (2 * np.pi / k0 / period)).astype(complex)
+        Kx = np.diag(kxn)
+        Vg, _ = _homogeneous_1d(kxn, 1.0, None)
+        Vr, Kzr = _homogeneous_1d(kxn, n_inc, pol)
+        Vt, Kzt = _homogeneous_1d(kxn, n_exit, pol)
+        Sg = _s_rt(I + np.diag(Vr / Vg), I - np.diag(Vr / Vg), True)
+    else:
+        raise ValueError(algo)
+    for e_conv, oe_conv, d in zip(e_convs[::-1], oe_convs[::-1], list(thicknesses)[::-1]):
+        if pol == 0:                                        # _base.py:142-148
+            lam, W = np.linalg.eig(Kx ** 2 - e_conv)
+            q = lam ** 0.5
+            V = W @ np.diag(q)
+        elif pol == 1:                                      # _base.py:150-159
+            E_i = np.linalg.inv(e_conv)
+            B = Kx @ E_i @ Kx - I
+            lam, W = np.linalg.eig(np.linalg.inv(oe_conv) @ B)
+            q = lam ** 0.5
+            V = oe_conv @ W @ np.diag(q)
+        else:
+            raise ValueError(pol)
+        if algo == 'TMM':                                   # transfer_1d_2
+            X = np.diag(np.exp(-k0 * q * d))
+            W_i, V_i = np.linalg.inv(W), np.linalg.inv(V)
+            a, b = 0.5 * (W_i @ f + V_i @ g), 0.5 * (W_i @ f - V_i @ g)
+            a_i = np.linalg.inv(a)
+            f, g, T = W @ (I + X @ b @ a_i @ X), V @ (I - X @ b @ a_i @ X), T @ a_i @ X
+        else:                                               # scattering_1d_2: A_B_matrices, S_layer, RedhefferStar
+            W_i, V_i = np.linalg.inv(W), np.linalg.inv(V)
+            A = W_i + V_i @ np.diag(Vg)
+            B = W_i - V_i @ np.diag(Vg)
+            X = np.diag(np.exp(-q * d * k0))
+            A_i = np.linalg.inv(A)
+            term_i = np.linalg.inv(A - X @ B @ A_i @ X @ B)
+            S11 = term_i @ (X @ B @ A_i @ X @ A - B)
+            S12 = term_i @ X @ (A - B @ A_i @ B)
+            Sg = _redheffer(Sg, dict(S11=S11, S22=S11, S12=S12, S21=S12))
+    if algo == 'TMM':                                       # transfer_1d_3
+        Tl = np.linalg.inv(g + 1j * YZ_I @ f) @ (1j * YZ_I @ delta + inc)
+        R = f @ Tl - delta
+        T = T @ Tl
+        de_ri = np.real(R * np.conj(R) * kz_inc / (k0 * n_inc * np.cos(theta)))
+        if pol == 0:
+            de_ti = np.real(T * np.conj(T) * kz_exit / (k0 * n_inc * np.cos(theta)))
+        else:
+            de_ti = np.real(T * np.conj(T) * kz_exit / n_exit ** 2) / (k0 * np.cos(theta) / n_inc)
+        return de_ri, de_ti
+    St = _s_rt(I + np.diag(Vt / Vg), I - np.diag(Vt / Vg), False)      # scattering_1d_3
+    Sg = _redheffer(Sg, St)
+    kinc_z = n_inc * np.cos(theta)
+    r = Sg['S11'] @ delta
+    t = Sg['S21'] @ delta
+    rsq, tsq = np.abs(r) ** 2, np.abs(t) ** 2
+    if pol == 0:
+        return np.real(Kzr) * rsq / np.real(kinc_z), np.real(Kzt) * tsq / np.real(kinc_z)
+    return np.real(Kzr) * rsq / np.real(kinc_z) / n_inc ** 2, np.real(Kzt) * tsq / np.real(kinc_z) * n_inc ** 2 / n_exit ** 4
+
+
+def evaluate_stack(structs, wavelength=1100.0, angle=60.0, order=40, thicknesses=(325.0,), pol=1, algo='TMM',
+                   n_ridge=None) -> OracleResult:
+    """structs: (L, n_cells) of +-1, one row per layer in the reference's list order (JLABCode with ucell of shape (L, 1, n),
+    JLAB/solver.py:16-38)."""
+    s = np.atleast_2d(np.asarray(structs, dtype=np.float64))
+    period = abs(wavelength / np.sin(angle / 180.0 * np.pi))
+    if n_ridge is None:
+        n_ridge = n_silicon_real(wavelength)
+    eps = (s + 1.0) / 2.0 * (n_ridge ** 2 - N_GROOVE ** 2) + N_GROOVE ** 2
+    e_convs = [toeplitz_from_cells(e, order) for e in eps]
+    oe_convs = [toeplitz_from_cells(1.0 / e, order) for e in eps]
+    de_ri, de_ti = solve_stack(e_convs, oe_convs, thicknesses, wavelength, period, order, pol, algo)
+    c = order
+    return OracleResult(eff=float(de_ti[c - 1]), refl_cut=de_ri[c - 1:c + 2][::-1].copy(), tran_cut=de_ti[c - 1:c + 2][::-1].copy(),
+                        de_ri=de_ri, de_ti=de_ti)

@@ -68,6 +68,7 @@ struct pirl_handle {
   bool regfront121 = false;   // ff = 121: padded register-tile front kernel, shared-memory kernels behind it
   // thread-block-cluster path (rcwa_cluster.cu): orders whose matrices do not fit one SM
   bool cluster = false; ClusterPlan cplan; double* cscratch = nullptr;
+  double* stack_params = nullptr;                // [max_batch][4] per-layer parameter rows of pirl_rcwa_eval_stack
   SmmPlan smm; double* smm_scratch = nullptr;    // cfg.algo == 1: scattering-matrix layer solve (rcwa_smm.cu)
   bool regtile = false; int rk_front_grid = 0; size_t rk_front_smem = 0; int rk_tail_grid = 0; size_t rk_tail_smem = 0;
   int last_chunk = 0;
@@ -160,11 +161,20 @@ static int mats_that_fit(size_t budget, size_t vec_bytes, size_t mat_bytes, int 
 
 extern "C" int pirl_rcwa_destroy(pirl_handle* h);
 
+// scattering-matrix kernel: planned at create for algo = 1 / TE handles, on the first layer-stack call otherwise
+static int smm_prepare(pirl_handle* h) {
+  if (h->smm.ok) return 0;
+  CUDA_TRY(smm_plan(h->ff, h->cfg.order, h->cfg.n_cells, h->sm_count, h->smem_optin - 1024, &h->smm));
+  if (!h->smm.ok) return fail(-9, "k_smm does not fit on this device");
+  CUDA_TRY(dmalloc(&h->smm_scratch, (size_t)h->smm.grid * h->smm.scratch_doubles));
+  return 0;
+}
+
 extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   if (!cfg || !out) return fail(-1, "null argument");
   if (cfg->order < 1 || cfg->order > 126) return fail(-2, "order must be in [1,126] (rotation column index is 8 bit)");
   if (cfg->n_cells < 2 || cfg->n_cells > 65536) return fail(-3, "n_cells out of range");
-  if (cfg->pol != 1) return fail(-4, "only TM (pol=1) is implemented: it is the only polarisation DeflectorGym evaluates");
+  if (cfg->pol != 1 && cfg->pol != 0) return fail(-4, "pol must be 1 (TM, what DeflectorGym evaluates) or 0 (TE)");
   if (cfg->theta_deg != 0.0) return fail(-5, "only normal incidence (theta=0) is implemented (real-symmetric formulation)");
   if (cfg->max_batch < 1) return fail(-6, "max_batch must be >= 1");
   if (cfg->algo != 0 && cfg->algo != 1) return fail(-10, "algo must be 0 (ETM / TMM) or 1 (SMM)");
@@ -287,7 +297,8 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   // the register-tile front kernels keep the twiddle table and the pattern of n_cells entries in shared memory: very long
   // patterns (about 10^4 cells and more) do not fit and run the generic kernels
   const size_t rk_budget = h->smem_optin - 1024;
-  if (ff == Cfg81::FF && !getenv("PIRL_NO_REGTILE") && (size_t)FrontSmem<Cfg81>::doubles(nc) * 8 <= rk_budget) {
+  const bool tm = cfg->pol == 1;      // TE runs the generic front kernels (standard symmetric eigenproblem) and k_smm
+  if (tm && ff == Cfg81::FF && !getenv("PIRL_NO_REGTILE") && (size_t)FrontSmem<Cfg81>::doubles(nc) * 8 <= rk_budget) {
     h->regtile = true;
     h->rk_front_smem = (size_t)FrontSmem<Cfg81>::doubles(nc) * 8;
     CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
@@ -310,7 +321,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     h->rk_tail2_grid = h->sm_count * per_sm;
     h->old_rktail = getenv("PIRL_OLD_RKTAIL") != nullptr;
   }
-  if (ff == Cfg121::FFR && !getenv("PIRL_NO_REGTILE") && (size_t)FrontSmem<Cfg121>::doubles(nc) * 8 <= rk_budget) {
+  if (tm && ff == Cfg121::FFR && !getenv("PIRL_NO_REGTILE") && (size_t)FrontSmem<Cfg121>::doubles(nc) * 8 <= rk_budget) {
     h->regfront121 = true;
     h->rk_front_smem = (size_t)FrontSmem<Cfg121>::doubles(nc) * 8;
     CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg121>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
@@ -328,7 +339,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
   }
   // cluster path: every order without a single-SM register-tile kernel whose padded matrix fits the 208 x 208 cluster tile
   // (PIRL_FORCE_CLUSTER=1: the 84 x 84 test variant for orders <= 41; PIRL_NO_CLUSTER=1: generic kernels)
-  if (!h->regtile && !h->regfront121 && !getenv("PIRL_NO_CLUSTER")) {
+  if (tm && !h->regtile && !h->regfront121 && !getenv("PIRL_NO_CLUSTER")) {
     const bool small = getenv("PIRL_FORCE_CLUSTER") != nullptr && ff <= 84;
     if (small || (ff > 81 && ff <= kClusterFF)) {
       CUDA_TRY(ck_plan(ff, nc, h->smem_optin, small, &h->cplan));
@@ -338,11 +349,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
       }
     }
   }
-  if (cfg->algo == 1) {
-    CUDA_TRY(smm_plan(ff, N, nc, h->sm_count, h->smem_optin - 1024, &h->smm));
-    if (!h->smm.ok) return fail(-9, "k_smm does not fit on this device");
-    CUDA_TRY(dmalloc(&h->smm_scratch, (size_t)h->smm.grid * h->smm.scratch_doubles));
-  }
+  if (cfg->algo == 1 || !tm) { if (int rc = smm_prepare(h)) return rc; }
   CUDA_TRY(max_carveout(k_front<FRONT_NT>)); CUDA_TRY(max_carveout(k_tridiag<TRI_NT>)); CUDA_TRY(max_carveout(k_ql));
   CUDA_TRY(max_carveout(k_apply<96, 4, 81>)); CUDA_TRY(max_carveout(k_apply<96, 4, 96>)); CUDA_TRY(max_carveout(k_apply<64, 2, 256>)); CUDA_TRY(max_carveout(k_apply<32, 2, 256>));
   CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 4>)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 8>));
@@ -390,7 +397,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   cudaFree(h->d_tw); cudaFree(h->d_Dk);
   cudaFree(h->Cbuf); cudaFree(h->Lbuf); cudaFree(h->Wbuf); cudaFree(h->tri); cudaFree(h->lam);
   cudaFree(h->rot_cs); cudaFree(h->sweeps); cudaFree(h->nrot); cudaFree(h->nsw); cudaFree(h->wstatus); cudaFree(h->scratch); cudaFree(h->phase_clk); cudaFree(h->trace); cudaFree(h->queues);
-  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status); cudaFree(h->cscratch); cudaFree(h->smm_scratch);
+  cudaFree(h->hd_patterns); cudaFree(h->hd_params); cudaFree(h->hd_out); cudaFree(h->hd_status); cudaFree(h->cscratch); cudaFree(h->smm_scratch); cudaFree(h->stack_params);
   cudaFree(h->g_lamb); cudaFree(h->g_Lf); cudaFree(h->g_Rf); cudaFree(h->g_Vf); cudaFree(h->g_Einv); cudaFree(h->g_scr_tail); cudaFree(h->g_scr_eig); cudaFree(h->hd_grad);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
@@ -476,7 +483,7 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
 }
 
 static void launch_tail(pirl_handle* h, KParams P, cudaStream_t st) {
-  if (h->cfg.algo == 1) {          // scattering-matrix form of the layer solve
+  if (h->cfg.algo == 1 || h->cfg.pol == 0) {          // scattering-matrix form of the layer solve (the only tail for TE)
     StageTimer t(h, 11, st);
     cudaError_t e = smm_launch(h->smm, P, h->smm_scratch, st);
     if (e != cudaSuccess && h->sync_fail_stage < 0) { h->sync_fail_stage = 11; h->sync_err = e; }
@@ -526,7 +533,7 @@ static KParams chunk_params(pirl_handle* h, const int8_t* patterns, const double
   KParams P;
   memset(&P, 0, sizeof(P));
   P.n_cells = h->cfg.n_cells; P.N = h->cfg.order; P.ff = h->ff; P.ld = h->ld; P.B = Bc;
-  P.n_inc = h->cfg.n_inc; P.n_exit = h->cfg.n_exit; P.eps_g = h->cfg.n_groove * h->cfg.n_groove;
+  P.n_inc = h->cfg.n_inc; P.n_exit = h->cfg.n_exit; P.eps_g = h->cfg.n_groove * h->cfg.n_groove; P.pol = h->cfg.pol;
   P.tw = h->d_tw; P.Dk = h->d_Dk; P.patterns = patterns; P.params = params; P.pstride = pstride;
   P.Cbuf = h->Cbuf; P.Lbuf = h->Lbuf; P.Wbuf = h->Wbuf; P.tri = h->tri; P.lam = h->lam;
   P.rot_cs = h->rot_cs; P.sweeps = h->sweeps; P.nrot = h->nrot; P.nsw = h->nsw; P.maxrot = h->maxrot; P.maxsw = h->maxsw;
@@ -710,6 +717,90 @@ extern "C" int pirl_rcwa_eval_host(pirl_handle* h, const int8_t* patterns, const
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// layer stacks (the reference's layer loop, _base.py:141): every (structure, layer) pair goes through the front kernels as
+// an independent eigenproblem, k_smm combines the layers of a structure with one Redheffer star product each
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_expand_params(const double* __restrict__ params, int pstride, const double* __restrict__ thick, int tstride,
+                                int L, long long BL, double* __restrict__ out) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= BL) return;
+  const long long b = idx / L;
+  const int l = (int)(idx - b * L);
+  const double* p = params + b * pstride;
+  out[4 * idx + 0] = p[0]; out[4 * idx + 1] = p[1]; out[4 * idx + 2] = thick[b * tstride + l]; out[4 * idx + 3] = p[3];
+}
+
+extern "C" int pirl_rcwa_eval_stack(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                                    const double* thickness, int32_t thickness_stride, int32_t n_layers, int64_t B, double* eff,
+                                    double* de_r3, double* de_t3, int32_t* status, void* stream) {
+  if (B == 0 && h) return 0;
+  if (!h || !patterns || !params || !thickness || !eff) return fail(-1, "null argument");
+  if (B < 0) return fail(-2, "negative batch");
+  if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
+  if (n_layers < 1 || n_layers > h->cfg.max_batch) return fail(-5, "n_layers must be in [1, max_batch]");
+  if (thickness_stride != 0 && thickness_stride != n_layers) return fail(-6, "thickness_stride must be 0 or n_layers");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  if (int rc = smm_prepare(h)) return rc;
+  if (!h->stack_params) CUDA_TRY(dmalloc(&h->stack_params, (size_t)h->cfg.max_batch * 4));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int L = n_layers, nc = h->cfg.n_cells;
+  const int64_t per = h->cfg.max_batch / L;
+  for (int64_t off = 0; off < B; off += per) {
+    const int Bc = (int)std::min<int64_t>(per, B - off);
+    const long long BL = (long long)Bc * L;
+    k_expand_params<<<(unsigned)((BL + 127) / 128), 128, 0, st>>>(params + off * param_stride, param_stride,
+                                                                  thickness + off * thickness_stride, thickness_stride, L, BL,
+                                                                  h->stack_params);
+    KParams P = chunk_params(h, patterns + off * L * nc, h->stack_params, 4, (int)BL, eff + off, nullptr, nullptr, nullptr);
+    launch_front(h, P, st);
+    launch_ql(h, P, st);
+    launch_apply(h, P, st);
+    KParams S = P;
+    S.B = Bc; S.n_layers = L; S.layer_rev = (h->cfg.algo == 1) ? 1 : 0;
+    S.de_r3 = de_r3 ? de_r3 + 3 * off : nullptr; S.de_t3 = de_t3 ? de_t3 + 3 * off : nullptr; S.status = status ? status + off : nullptr;
+    {
+      StageTimer t(h, 11, st);
+      cudaError_t e = smm_launch(h->smm, S, h->smm_scratch, st);
+      if (e != cudaSuccess && h->sync_fail_stage < 0) { h->sync_fail_stage = 11; h->sync_err = e; }
+      h->launches += 2;
+    }
+    h->last_chunk = (int)BL;
+    if (h->sync_fail_stage >= 0)
+      return fail((int)h->sync_err, std::string("kernel ") + kStageNames[h->sync_fail_stage] + ": " + cudaGetErrorString(h->sync_err));
+    CUDA_TRY(cudaGetLastError());
+  }
+  return 0;
+}
+
+extern "C" int pirl_rcwa_eval_stack_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
+                                         const double* thickness, int32_t thickness_stride, int32_t n_layers, int64_t B,
+                                         double* eff, double* de_r3, double* de_t3, int32_t* status) {
+  if (B == 0 && h) return 0;
+  if (!h || !patterns || !params || !thickness || !eff) return fail(-1, "null argument");
+  if (B < 0 || n_layers < 1) return fail(-2, "bad batch / layer count");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const size_t nc = h->cfg.n_cells, L = n_layers;
+  const size_t np = param_stride ? (size_t)B * 4 : 4, nt = thickness_stride ? (size_t)B * L : L;
+  int8_t* d_pat = nullptr; double* d_par = nullptr; double* d_th = nullptr; double* d_out = nullptr; int32_t* d_st = nullptr;
+  struct Free { int8_t*& a; double*& b; double*& c; double*& d; int32_t*& e;
+                ~Free() { cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e); } } guard{d_pat, d_par, d_th, d_out, d_st};
+  CUDA_TRY(dmalloc(&d_pat, (size_t)B * L * nc)); CUDA_TRY(dmalloc(&d_par, np)); CUDA_TRY(dmalloc(&d_th, nt));
+  CUDA_TRY(dmalloc(&d_out, (size_t)B * 7)); CUDA_TRY(dmalloc(&d_st, (size_t)B));
+  cudaStream_t st = h->own_stream;
+  CUDA_TRY(cudaMemcpyAsync(d_pat, patterns, (size_t)B * L * nc, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(d_par, params, np * sizeof(double), cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(d_th, thickness, nt * sizeof(double), cudaMemcpyHostToDevice, st));
+  int rc = pirl_rcwa_eval_stack(h, d_pat, d_par, param_stride, d_th, thickness_stride, n_layers, B, d_out, d_out + B, d_out + 4 * B, d_st, st);
+  if (rc) { cudaStreamSynchronize(st); return rc; }
+  CUDA_TRY(cudaMemcpyAsync(eff, d_out, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (de_r3) CUDA_TRY(cudaMemcpyAsync(de_r3, d_out + B, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (de_t3) CUDA_TRY(cudaMemcpyAsync(de_t3, d_out + 4 * B, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (status) CUDA_TRY(cudaMemcpyAsync(status, d_st, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return 0;
+}
+
 extern "C" int pirl_env_flip(int8_t* patterns, const int64_t* actions, int64_t B, int32_t n_cells, void* stream) {
   if (!patterns || !actions) return fail(-1, "null argument");
   if (B <= 0) return 0;
@@ -854,7 +945,7 @@ extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const
   if (B < 0) return fail(-2, "negative batch");
   if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
   CUDA_TRY(cudaSetDevice(h->cfg.device));
-  if (h->cfg.algo != 0) return fail(-4, "the adjoint gradient is implemented for algo = 0 (ETM) only");
+  if (h->cfg.algo != 0 || h->cfg.pol != 1) return fail(-4, "the adjoint gradient is implemented for algo = 0 (ETM), TM only");
   if (int rc = grad_prepare(h)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t mb = h->cfg.max_batch;

@@ -36,6 +36,9 @@ struct KParams {
   int smem_mats;              // how many (kernel-specific) matrices live in shared memory
   int* queue;                 // optional work counter (zeroed before the launch): persistent CTAs fetch structures dynamically
   double* Einv;               // optional [B][ff][ff]: E^-1 exported by the front kernels for the adjoint sweep (null otherwise)
+  int pol;                    // 1 = TM (default), 0 = TE (_base.py:142-148): generic front kernels + k_smm only
+  int n_layers;               // k_smm: layers per structure (entries b * n_layers + l of the per-layer workspaces)
+  int layer_rev;              // k_smm: star products taken in reversed list order (the reference's 'SMM' loop, _base.py:141)
   // outputs
   double* eff; double* de_r3; double* de_t3; int* status;
 };

@@ -63,6 +63,23 @@ __global__ void __launch_bounds__(NT) k_front(KParams P) {
       }
     }
     __syncthreads();
+    if (P.pol == 0) {
+      // TE (_base.py:142-148): A = Kx^2 - E is real symmetric in the real basis -> a STANDARD symmetric eigenproblem:
+      // C = Kx^2 - E goes straight to the tridiagonalisation, the factor is the identity (W orthonormal, V = W Q)
+      const double de = er - eg;
+      double* Cg = P.Cbuf + (size_t)b * ff * ff;
+      double* Lg = P.Lbuf + (size_t)b * ff * ff;
+      for (int i = warp; i < ff; i += NW) {
+        const double kap = (i < z) ? ((i >> 1) + 1) * sa : 0.0;
+        for (int j = lane; j < ff; j += 32) {
+          const double dl = (i == j) ? 1.0 : 0.0;
+          Cg[i * ff + j] = kap * kap * dl - fma(de, basis_toeplitz(i, j, N, cre, cim), eg * dl);
+          Lg[i * ff + j] = dl;
+        }
+      }
+      if (tid == 0) P.wstatus[b] = 0;
+      continue;
+    }
     // ---- E = eps_g I + (eps_r - eps_g) T(c),  A = I/eps_g + (1/eps_r - 1/eps_g) T(c) (real basis) ----
     {
       const double de = er - eg, da = 1.0 / er - 1.0 / eg, ia = 1.0 / eg;

@@ -10,12 +10,14 @@
 // kx^2 only), so every block is the reference's block conjugated by that unitary and the efficiencies are identical.
 // One CTA per structure, blocks in an L2-resident per-CTA scratch.  This is the reference's slower variant (1.6x-2.9x its
 // TMM) and is not tuned: it exists so that algo = 'SMM' is a real operator, and as the stable form for
-// multilayer stacks.
+// multilayer stacks: P.n_layers > 1 takes one more star product per layer (entries b * n_layers + l of the per-layer
+// workspaces; list order, or reversed list order when P.layer_rev is set -- the reference's 'SMM' loop walks the list
+// backwards, _base.py:141).  P.pol = 0 is the TE case (_base.py:142-148): orthonormal modes, V = W Q, no n^2 factors.
 #pragma once
 #include "rcwa_common.cuh"
 
 constexpr int SMM_NT = 256;
-constexpr int SMM_NMAT = 20;          // complex ff x ff blocks of per-CTA scratch
+constexpr int SMM_NMAT = 21;          // complex ff x ff blocks of per-CTA scratch
 
 __host__ __device__ inline size_t smm_scratch_doubles(int ff) { return (size_t)SMM_NMAT * 2 * ff * ff + 2 * (size_t)ff * ff; }
 // shared: cre, cim [2N+1], per-harmonic complex diagonals vg, vr, vt, kzr, kzt, q, X [ff each], pattern bits, pivot slot
@@ -173,6 +175,8 @@ __device__ __forceinline__ void smm_homogeneous(double kap, double n_index, bool
 __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ smm_scratch) {
   extern __shared__ __align__(16) double sm[];
   const int ff = P.ff, N = P.N, z = 2 * N, nc = P.n_cells, n = ff;
+  const int L = P.n_layers > 0 ? P.n_layers : 1;
+  const bool tm = P.pol != 0;
   const int tid = threadIdx.x;
   double* cre = sm;
   double* cim = cre + (2 * N + 1);
@@ -194,79 +198,24 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
 
   for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
     __syncthreads();
-    const double* pr = P.params + (size_t)b * P.pstride;
-    const double wl = pr[0], thick = pr[2], nr = pr[3];
-    const double sa = sin(pr[1] * (3.14159265358979323846 / 180.0));
-    const double k0d = 2.0 * 3.14159265358979323846 / wl * thick;
-    const double nI = P.n_inc, nII = P.n_exit, er = nr * nr, eg = P.eps_g;
-    for (int p = tid; p < nc; p += SMM_NT) su[p] = P.patterns[(size_t)b * nc + p] > 0;
-    __syncthreads();
-    // Fourier coefficients of the pattern (same closed form as the front kernels; convolution_matrix.py:101-114)
-    for (int k = tid; k <= 2 * N; k += SMM_NT) {
-      double sx = 0.0, sy = 0.0;
-      int idx = 0;
-      const int km = k % nc;
-      for (int p = 0; p < nc; ++p) {
-        if (su[p]) { const cplx w = __ldg(&P.tw[idx]); sx += w.x; sy += w.y; }
-        idx += km; if (idx >= nc) idx -= nc;
-      }
-      const cplx d = __ldg(&P.Dk[k]);
-      cre[k] = sx * d.x - sy * d.y;
-      cim[k] = sx * d.y + sy * d.x;
-    }
-    // per-harmonic media (scattering_1d_1, scattering_method.py:12-31), per-mode q and X (S_layer, smm_util.py:55)
-    const double* lam = P.lam + (size_t)b * ff;
+    const double* pr0 = P.params + (size_t)b * L * P.pstride;          // (wavelength, angle) are those of the structure's first entry
+    const double wl = pr0[0];
+    const double sa = sin(pr0[1] * (3.14159265358979323846 / 180.0));
+    const double nI = P.n_inc, nII = P.n_exit, eg = P.eps_g;
+    // per-harmonic media (scattering_1d_1, scattering_method.py:12-31)
     for (int j = tid; j < ff; j += SMM_NT) {
       const double kap = (j < z) ? ((j >> 1) + 1) * sa : 0.0;
       cplx dummy;
       smm_homogeneous(kap, 1.0, false, &vg[j], &dummy);               // gap medium, pol = None
-      smm_homogeneous(kap, nI, true, &vr[j], &kzr[j]);
-      smm_homogeneous(kap, nII, true, &vt[j], &kzt[j]);
-      const double l = lam[j];
-      if (l >= 0.0) { const double s = sqrt(l); qv[j] = make_double2(s, 0.0); Xv[j] = make_double2(exp(-k0d * s), 0.0); }
-      else { const double s = sqrt(-l); double sn, cn; sincos(k0d * s, &sn, &cn); qv[j] = make_double2(0.0, s); Xv[j] = make_double2(cn, -sn); }
+      smm_homogeneous(kap, nI, tm, &vr[j], &kzr[j]);
+      smm_homogeneous(kap, nII, tm, &vt[j], &kzt[j]);
     }
     __syncthreads();
-    // E^- in the real basis; W^-1 = W^T E^- (the modes are E^- -orthonormal: W^T E^- W = I)
-    {
-      const double da = 1.0 / er - 1.0 / eg, ia = 1.0 / eg;
-      for (int idx = tid; idx < n * n; idx += SMM_NT) {
-        const int i = idx / n, j = idx - i * n;
-        Amat[idx] = fma(da, basis_toeplitz(i, j, N, cre, cim), (i == j) ? ia : 0.0);
-      }
-    }
-    __syncthreads();
-    const double* Wg = P.Wbuf + (size_t)b * ff * ff;
     cplx *A = M[0], *B = M[1], *Ai = M[2], *T0 = M[3], *T1 = M[4], *T2 = M[5], *T3 = M[6], *SL11 = M[7], *SL12 = M[8];
-    // A_B_matrices (smm_util.py:24-39) with Wg = I: A = W^-1 + V^-1 Vg, B = W^-1 - V^-1 Vg, V^-1 = Q^-1 W^T
-    for (int idx = tid; idx < n * n; idx += SMM_NT) {
-      const int m = idx / n, j = idx - m * n;
-      double winv = 0.0;
-      for (int i = 0; i < n; ++i) winv = fma(Wg[(size_t)i * n + m], Amat[(size_t)i * n + j], winv);
-      const cplx vi = cscale(cmul(cinv(qv[m]), vg[j]), Wg[(size_t)j * n + m]);
-      A[idx] = make_double2(winv + vi.x, vi.y);
-      B[idx] = make_double2(winv - vi.x, -vi.y);
-    }
-    __syncthreads();
-    bool sing = false;
-    // S_layer (smm_util.py:42-67)
-    smm_axpby(T0, 1.0, A, 0.0, nullptr, 0.0, n, tid);
-    sing |= smm_inverse(Ai, T0, n, tid, slot);                  // A_i
-    smm_gemm(T0, B, Ai, n, tid);
-    smm_scale(T1, Xv, T0, Xv, n, tid);                          // T1 = X B A_i X
-    smm_gemm(T2, T1, B, n, tid);
-    smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - X B A_i X B
-    sing |= smm_inverse(T3, T2, n, tid, slot);                  // term_i
-    smm_gemm(T0, T1, A, n, tid);
-    smm_axpby(T0, 1.0, T0, -1.0, B, 0.0, n, tid);
-    smm_gemm(SL11, T3, T0, n, tid);                             // S11 = S22
-    smm_gemm(T0, Ai, B, n, tid);
-    smm_gemm(T2, B, T0, n, tid);
-    smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - B A_i B
-    smm_scale(T0, Xv, T2, nullptr, n, tid);
-    smm_gemm(SL12, T3, T0, n, tid);                             // S12 = S21
-    // S_RT of the reflection region (A_B_matrices_half_space + S_RT, ref_mode = True): diagonal blocks, kept as matrices
     cplx* R[4] = {M[9], M[10], M[11], M[12]};
+    cplx* G[4] = {M[13], M[14], M[15], M[16]};
+    cplx* H[4] = {M[17], M[18], M[19], M[20]};
+    // S_RT of the reflection region (A_B_matrices_half_space + S_RT, ref_mode = True): diagonal blocks, kept as matrices
     for (int idx = tid; idx < n * n; idx += SMM_NT) {
       const int i = idx / n, j = idx - i * n;
       cplx s11 = make_double2(0, 0), s12 = s11, s21 = s11, s22 = s11;
@@ -281,9 +230,82 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
       R[0][idx] = s11; R[1][idx] = s12; R[2][idx] = s21; R[3][idx] = s22;
     }
     __syncthreads();
-    cplx* G[4] = {M[13], M[14], M[15], M[16]};
-    cplx* L[4] = {SL11, SL12, SL12, SL11};
-    sing |= smm_redheffer(G, R, L, T0, T1, T2, T3, n, tid, slot);       // Sg = S_ref (*) S_layer   (scattering_1d_2)
+    bool sing = false;
+    int wst = 0;
+    int cur = 0;                          // global matrix so far: 0 = R (reflection region only), 1 = G, 2 = H
+    for (int step = 0; step < L; ++step) {
+      const int l = P.layer_rev ? L - 1 - step : step;
+      const size_t e = (size_t)b * L + l;                               // entry of this layer in the per-layer workspaces
+      const double* pr = P.params + e * P.pstride;
+      const double thick = pr[2], nr = pr[3], er = nr * nr;
+      const double k0d = 2.0 * 3.14159265358979323846 / wl * thick;
+      const double* lam = P.lam + e * ff;
+      const double* Wg = P.Wbuf + e * ff * ff;
+      wst |= P.wstatus[e];
+      for (int j = tid; j < ff; j += SMM_NT) {                          // per-mode q and X (S_layer, smm_util.py:55)
+        const double lm = lam[j];
+        if (lm >= 0.0) { const double s = sqrt(lm); qv[j] = make_double2(s, 0.0); Xv[j] = make_double2(exp(-k0d * s), 0.0); }
+        else { const double s = sqrt(-lm); double sn, cn; sincos(k0d * s, &sn, &cn); qv[j] = make_double2(0.0, s); Xv[j] = make_double2(cn, -sn); }
+      }
+      if (tm) {
+        // E^- of this layer in the real basis (closed-form Fourier coefficients, convolution_matrix.py:101-114);
+        // W^-1 = W^T E^- (the TM modes are E^- -orthonormal: W^T E^- W = I)
+        for (int p = tid; p < nc; p += SMM_NT) su[p] = P.patterns[e * nc + p] > 0;
+        __syncthreads();
+        for (int k = tid; k <= 2 * N; k += SMM_NT) {
+          double sx = 0.0, sy = 0.0;
+          int idx = 0;
+          const int km = k % nc;
+          for (int p = 0; p < nc; ++p) {
+            if (su[p]) { const cplx w = __ldg(&P.tw[idx]); sx += w.x; sy += w.y; }
+            idx += km; if (idx >= nc) idx -= nc;
+          }
+          const cplx d = __ldg(&P.Dk[k]);
+          cre[k] = sx * d.x - sy * d.y;
+          cim[k] = sx * d.y + sy * d.x;
+        }
+        __syncthreads();
+        const double da = 1.0 / er - 1.0 / eg, ia = 1.0 / eg;
+        for (int idx = tid; idx < n * n; idx += SMM_NT) {
+          const int i = idx / n, j = idx - i * n;
+          Amat[idx] = fma(da, basis_toeplitz(i, j, N, cre, cim), (i == j) ? ia : 0.0);
+        }
+      }
+      __syncthreads();
+      // A_B_matrices (smm_util.py:24-39) with Wg = I: A = W^-1 + V^-1 Vg, B = W^-1 - V^-1 Vg, V^-1 = Q^-1 W^T (TM: V = E^- W Q
+      // with W^T E^- W = I; TE: V = W Q with W^T W = I)
+      for (int idx = tid; idx < n * n; idx += SMM_NT) {
+        const int m = idx / n, j = idx - m * n;
+        double winv = 0.0;
+        if (tm) { for (int i = 0; i < n; ++i) winv = fma(Wg[(size_t)i * n + m], Amat[(size_t)i * n + j], winv); }
+        else winv = Wg[(size_t)j * n + m];
+        const cplx vi = cscale(cmul(cinv(qv[m]), vg[j]), Wg[(size_t)j * n + m]);
+        A[idx] = make_double2(winv + vi.x, vi.y);
+        B[idx] = make_double2(winv - vi.x, -vi.y);
+      }
+      __syncthreads();
+      // S_layer (smm_util.py:42-67)
+      smm_axpby(T0, 1.0, A, 0.0, nullptr, 0.0, n, tid);
+      sing |= smm_inverse(Ai, T0, n, tid, slot);                  // A_i
+      smm_gemm(T0, B, Ai, n, tid);
+      smm_scale(T1, Xv, T0, Xv, n, tid);                          // T1 = X B A_i X
+      smm_gemm(T2, T1, B, n, tid);
+      smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - X B A_i X B
+      sing |= smm_inverse(T3, T2, n, tid, slot);                  // term_i
+      smm_gemm(T0, T1, A, n, tid);
+      smm_axpby(T0, 1.0, T0, -1.0, B, 0.0, n, tid);
+      smm_gemm(SL11, T3, T0, n, tid);                             // S11 = S22
+      smm_gemm(T0, Ai, B, n, tid);
+      smm_gemm(T2, B, T0, n, tid);
+      smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - B A_i B
+      smm_scale(T0, Xv, T2, nullptr, n, tid);
+      smm_gemm(SL12, T3, T0, n, tid);                             // S12 = S21
+      cplx* Lm[4] = {SL11, SL12, SL12, SL11};
+      // Sg = Sg (*) S_layer   (scattering_1d_2)
+      if (cur == 0) { sing |= smm_redheffer(G, R, Lm, T0, T1, T2, T3, n, tid, slot); cur = 1; }
+      else if (cur == 1) { sing |= smm_redheffer(H, G, Lm, T0, T1, T2, T3, n, tid, slot); cur = 2; }
+      else { sing |= smm_redheffer(G, H, Lm, T0, T1, T2, T3, n, tid, slot); cur = 1; }
+    }
     // transmission region (ref_mode = False: blocks swapped)
     for (int idx = tid; idx < n * n; idx += SMM_NT) {
       const int i = idx / n, j = idx - i * n;
@@ -299,8 +321,9 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
       R[0][idx] = s22; R[1][idx] = s21; R[2][idx] = s12; R[3][idx] = s11;
     }
     __syncthreads();
-    cplx* F[4] = {M[0], M[1], M[2], M[17]};
-    sing |= smm_redheffer(F, G, R, T0, T1, T2, T3, n, tid, slot);       // Sg = Sg (*) S_trn        (scattering_1d_3)
+    cplx* const* F;
+    if (cur == 1) { sing |= smm_redheffer(H, G, R, T0, T1, T2, T3, n, tid, slot); F = H; }     // Sg = Sg (*) S_trn  (scattering_1d_3)
+    else { sing |= smm_redheffer(G, H, R, T0, T1, T2, T3, n, tid, slot); F = G; }
     // fields of the incident zeroth order (c_inc = delta: W_r = I) and efficiencies of orders -1, 0, +1
     if (tid == 0) {
       const cplx Rc = F[0][(size_t)0 * n + z], Rs = F[0][(size_t)1 * n + z], R0 = F[0][(size_t)z * n + z];
@@ -310,16 +333,18 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
       const cplx Tp = make_double2((Tc.x + Ts.y) * is2, (Tc.y - Ts.x) * is2);
       const cplx Rm = make_double2((Rc.x - Rs.y) * is2, (Rc.y + Rs.x) * is2);
       const cplx Rp = make_double2((Rc.x + Rs.y) * is2, (Rc.y - Rs.x) * is2);
-      // de_ri = Re(Kzr) |r|^2 / Re(k_inc_z) / n_I^2 ; de_ti = Re(Kzt) |t|^2 / Re(k_inc_z) n_I^2 / n_II^4   (scattering_method.py:66-69)
+      // TM: de_ri = Re(Kzr) |r|^2 / Re(k_inc_z) / n_I^2 ; de_ti = Re(Kzt) |t|^2 / Re(k_inc_z) n_I^2 / n_II^4 ; TE: without the
+      // index factors   (scattering_method.py:62-69)
       const double kinc = nI;
+      const double fr = tm ? 1.0 / (nI * nI) : 1.0, ft = tm ? (nI * nI) / (nII * nII * nII * nII) : 1.0;
       double der[3], det[3];
-      der[0] = kzr[0].x * (Rm.x * Rm.x + Rm.y * Rm.y) / kinc / (nI * nI);
-      der[1] = kzr[z].x * (R0.x * R0.x + R0.y * R0.y) / kinc / (nI * nI);
-      der[2] = kzr[0].x * (Rp.x * Rp.x + Rp.y * Rp.y) / kinc / (nI * nI);
-      det[0] = kzt[0].x * (Tm.x * Tm.x + Tm.y * Tm.y) / kinc * (nI * nI) / (nII * nII * nII * nII);
-      det[1] = kzt[z].x * (T0c.x * T0c.x + T0c.y * T0c.y) / kinc * (nI * nI) / (nII * nII * nII * nII);
-      det[2] = kzt[0].x * (Tp.x * Tp.x + Tp.y * Tp.y) / kinc * (nI * nI) / (nII * nII * nII * nII);
-      int st = P.wstatus[b];
+      der[0] = kzr[0].x * (Rm.x * Rm.x + Rm.y * Rm.y) / kinc * fr;
+      der[1] = kzr[z].x * (R0.x * R0.x + R0.y * R0.y) / kinc * fr;
+      der[2] = kzr[0].x * (Rp.x * Rp.x + Rp.y * Rp.y) / kinc * fr;
+      det[0] = kzt[0].x * (Tm.x * Tm.x + Tm.y * Tm.y) / kinc * ft;
+      det[1] = kzt[z].x * (T0c.x * T0c.x + T0c.y * T0c.y) / kinc * ft;
+      det[2] = kzt[0].x * (Tp.x * Tp.x + Tp.y * Tp.y) / kinc * ft;
+      int st = wst;
       if (sing || !isfinite(det[0]) || !isfinite(det[1]) || !isfinite(der[1])) st |= PIRL_ST_NONFINITE_;
       P.eff[b] = det[0];
       if (P.de_r3) { P.de_r3[3 * b] = der[0]; P.de_r3[3 * b + 1] = der[1]; P.de_r3[3 * b + 2] = der[2]; }

@@ -41,6 +41,7 @@ class RCWABatch:
         self.device = torch.device("cuda", device if isinstance(device, int) else torch.device(device).index or 0)
         self.n_cells, self.order, self.ff = int(n_cells), int(order), 2 * int(order) + 1
         self.n_I, self.n_II, self.n_groove = float(n_I), float(n_II), float(n_groove)
+        self.pol = int(pol)
         if algo not in ('TMM', 'SMM', 0, 1):
             raise ValueError(algo)                       # rcwa.py:31-32
         self.algo = 1 if algo in ('SMM', 1) else 0       # 'TMM': enhanced transmittance matrices; 'SMM': Redheffer star products
@@ -153,6 +154,35 @@ class RCWABatch:
             return eff, r3, t3, st
         return eff
 
+    def evaluate_stack_host(self, patterns, wavelength=1100.0, angle=60.0, thicknesses=(325.0,), n_ridge=None,
+                            return_orders=False):
+        """Layer stacks (the reference's layer loop, _base.py:141): patterns numpy [B, L, n_cells] (>0 = ridge), layers in the
+        reference's list order; ``thicknesses`` [L] (shared) or [B, L].  Host buffers in and out (``pirl_rcwa_eval_stack_host``).
+        The layer ORDER convention follows the handle's ``algo`` like the reference does ('SMM' = reversed list)."""
+        pats = np.asarray(patterns)
+        if pats.ndim != 3 or pats.shape[2] != self.n_cells:
+            raise ValueError(f"patterns must be [B, L, {self.n_cells}]")
+        B, L = pats.shape[0], pats.shape[1]
+        p8 = np.ascontiguousarray(np.where(pats > 0, 1, -1).astype(np.int8))
+        rows, stride = self._params(B, wavelength, angle, 0.0, n_ridge)
+        th = np.ascontiguousarray(np.asarray(thicknesses, dtype=np.float64))
+        if th.shape == (L,):
+            tstride = 0
+        elif th.shape == (B, L):
+            tstride = L
+        else:
+            raise ValueError(f"thicknesses must have shape ({L},) or ({B}, {L})")
+        eff = np.empty(B, dtype=np.float64)
+        st = np.empty(B, dtype=np.int32)
+        r3 = np.empty((B, 3), dtype=np.float64) if return_orders else None
+        t3 = np.empty((B, 3), dtype=np.float64) if return_orders else None
+        _lib.check(self.lib.pirl_rcwa_eval_stack_host(
+            self._h, p8.ctypes.data, rows.ctypes.data, stride, th.ctypes.data, tstride, L, B, eff.ctypes.data,
+            r3.ctypes.data if return_orders else None, t3.ctypes.data if return_orders else None, st.ctypes.data))
+        if return_orders:
+            return eff, r3, t3, st
+        return eff
+
     def evaluate_grad(self, patterns, wavelength=1100.0, angle=60.0, thickness=325.0, n_ridge=None, params=None):
         """Efficiency and its adjoint gradient d eff / d s_p.  patterns: torch int8 CUDA tensor [B, n_cells] of +-1.
         Returns (eff [B], grad [B, n_cells], status [B]) as CUDA tensors, asynchronous on the current torch stream.
@@ -235,15 +265,15 @@ _backends = {}
 _backends_lock = threading.Lock()
 
 
-def shared_backend(n_cells, order, n_I=1.45, n_II=1.0, n_groove=1.0, max_batch=4096, device=None, algo='TMM') -> RCWABatch:
+def shared_backend(n_cells, order, n_I=1.45, n_II=1.0, n_groove=1.0, max_batch=4096, device=None, algo='TMM', pol=1) -> RCWABatch:
     """One cached handle per configuration (the reference builds a solver object per call; here the
     workspaces are allocated once)."""
     torch = _torch()
     dev = torch.cuda.current_device() if device is None else device
-    key = (int(n_cells), int(order), float(n_I), float(n_II), float(n_groove), int(max_batch), dev, algo)
+    key = (int(n_cells), int(order), float(n_I), float(n_II), float(n_groove), int(max_batch), dev, algo, int(pol))
     with _backends_lock:
         if key not in _backends:
-            _backends[key] = RCWABatch(n_cells, order, n_I, n_II, n_groove, max_batch=max_batch, device=dev, algo=algo)
+            _backends[key] = RCWABatch(n_cells, order, n_I, n_II, n_groove, pol=pol, max_batch=max_batch, device=dev, algo=algo)
         return _backends[key]
 
 
@@ -258,8 +288,9 @@ class JLABCode:
                  thickness=(325,), algo='TMM'):
         if grating_type != 0:
             raise ValueError("only grating_type=0 (1D) is on the accelerated path")
-        if pol != 1:
-            raise ValueError("only pol=1 (TM) is on the accelerated path")
+        if pol not in (0, 1):
+            raise ValueError(pol)                        # _base.py:160-161
+        self.pol = pol
         if algo not in ('TMM', 'SMM'):
             raise ValueError(algo)
         if theta != 0 or phi != 0:
@@ -271,10 +302,10 @@ class JLABCode:
         self.wls = np.atleast_1d(np.asarray(wls, dtype=np.float64))
         self.ucell = np.asarray(ucell, dtype=np.float64)
         self.thickness = np.atleast_1d(np.asarray(thickness, dtype=np.float64))
-        if self.ucell.ndim != 3 or self.ucell.shape[0] != 1 or self.ucell.shape[1] != 1:
-            raise ValueError("ucell must have shape (1, 1, n_cells): one layer, 1D")
-        if self.thickness.size != 1 or self.wls.size != 1:
-            raise ValueError("one layer / one wavelength per call")
+        if self.ucell.ndim != 3 or self.ucell.shape[1] != 1:
+            raise ValueError("ucell must have shape (n_layers, 1, n_cells): 1D layers")
+        if self.thickness.size != self.ucell.shape[0] or self.wls.size != 1:
+            raise ValueError("one thickness per layer / one wavelength per call")
 
     def reproduce_acs_cell(self, n_ridge, n_groove):
         wl = float(self.wls[0])
@@ -286,9 +317,14 @@ class JLABCode:
         # period = wl / sin(angle)  ->  the kernels take the deflection angle
         ratio = wl / float(self.period[0])
         angle = np.degrees(np.arcsin(ratio))
-        be = shared_backend(struct.size, self.fourier_order, self.n_I, self.n_II, float(n_groove), max_batch=64, algo=self.algo)
-        eff, r3, t3, st = be.evaluate_host(struct[None, :], wl, angle, float(self.thickness[0]), float(n_ridge),
-                                           return_orders=True)
+        be = shared_backend(struct.size, self.fourier_order, self.n_I, self.n_II, float(n_groove), max_batch=64, algo=self.algo,
+                            pol=self.pol)
+        if self.ucell.shape[0] > 1:          # layer stack (_base.py:141), layers in list order
+            eff, r3, t3, st = be.evaluate_stack_host(self.ucell[None, :, 0, :], wl, angle, self.thickness, float(n_ridge),
+                                                     return_orders=True)
+        else:
+            eff, r3, t3, st = be.evaluate_host(struct[None, :], wl, angle, float(self.thickness[0]), float(n_ridge),
+                                               return_orders=True)
         if st[0] & (ST_EIG_NOT_CONVERGED | ST_NOT_POSDEF):
             raise np.linalg.LinAlgError(f"RCWA solve failed, status {int(st[0])}")
         return float(eff[0]), r3[0, ::-1].copy(), t3[0, ::-1].copy()

@@ -502,3 +502,45 @@ def test_smm_scattering_matrix_operator(golden_dir, pkg, torch_mod):
     eff, refl, tran = code.reproduce_acs_cell('p_si__real', 1)
     assert abs(eff - float(g["G1_rand256_N40_SMM/ref_eff"])) <= 1e-12
     assert np.abs(tran - g["G1_rand256_N40_SMM/ref_tran_cut"]).max() <= 1e-12 and np.abs(refl - g["G1_rand256_N40_SMM/ref_refl_cut"]).max() <= 1e-12
+
+
+def test_layer_stacks_and_te_against_the_unmodified_reference(golden_dir, pkg):
+    """SURVEY section 8f rank 4, partly: multilayer stacks (_base.py:141) and TE polarisation (_base.py:142-148) through
+    pirl_rcwa_eval_stack / the TE front + k_smm, against fixtures written by oracle/make_stack_golden.py from the unmodified
+    reference (JLABCode with ucell of shape (L, 1, n)), for 'TMM' and 'SMM' -- including the reference's layer-order quirk
+    (its SMM result of a list equals its TMM result of the reversed list) -- through RCWABatch and the JLABCode drop-in."""
+    g = np.load(os.path.join(golden_dir, "rcwa_stack_golden.npz"))
+    names = sorted({k.split("/")[0] for k in g.files})
+    assert len(names) == 10
+    worst = 0.0
+    for n in names:
+        structs = g[n + "/structs"]
+        wl, ang, order = float(g[n + "/wavelength"]), float(g[n + "/angle"]), int(g[n + "/order"])
+        th, pol, algo = g[n + "/thickness"], int(g[n + "/pol"]), str(g[n + "/algo"])
+        be = pkg.RCWABatch(structs.shape[1], order, pol=pol, max_batch=16, device=0, algo=algo)
+        eff, r3, t3, st = be.evaluate_stack_host(structs[None], wl, ang, th, return_orders=True)
+        assert st[0] == 0, (n, st)
+        e = max(abs(eff[0] - float(g[n + "/ref_eff"])), np.abs(t3[0][::-1] - g[n + "/ref_tran_cut"]).max(),
+                np.abs(r3[0][::-1] - g[n + "/ref_refl_cut"]).max())
+        worst = max(worst, e)
+        assert e <= TIGHT, (n, e)
+        if structs.shape[0] == 1:            # single layer: the plain entry point must agree with the stack entry point
+            e1 = be.evaluate_host(structs[0][None], wl, ang, float(th[0]))
+            assert abs(e1[0] - eff[0]) <= 1e-12
+        code = pkg.JLABCode(n_I=1.45, n_II=1., theta=0, phi=0, fourier_order=order, period=[abs(wl / np.sin(ang / 180 * np.pi))],
+                            wls=np.array([wl]), pol=pol, ucell=structs[:, None, :], thickness=th, algo=algo)
+        ej, refl, tran = code.reproduce_acs_cell('p_si__real', 1)
+        assert abs(ej - float(g[n + "/ref_eff"])) <= TIGHT and np.abs(tran - g[n + "/ref_tran_cut"]).max() <= TIGHT
+        be.close()
+    # batch of stacks with per-structure thicknesses vs the oracle restatement (pinned to the reference above)
+    from oracle import rcwa_oracle as O
+    rng = np.random.default_rng(9)
+    pats = np.repeat(rng.choice([-1, 1], (5, 3, 16)), 16, axis=2)
+    ths = rng.uniform(60.0, 300.0, (5, 3))
+    be = pkg.RCWABatch(256, 24, max_batch=8, device=0)              # 15 layer problems > max_batch: chunked by structure
+    eff, r3, t3, st = be.evaluate_stack_host(pats, 1050.0, 55.0, ths, return_orders=True)
+    assert not st.any()
+    for i in range(5):
+        r = O.evaluate_stack(pats[i].astype(float), 1050.0, 55.0, 24, ths[i], 1, 'TMM')
+        assert abs(eff[i] - r.eff) <= TIGHT and np.abs(t3[i] - r.de_ti[23:26]).max() <= TIGHT
+    be.close()

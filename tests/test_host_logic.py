@@ -113,7 +113,7 @@ def test_create_fails_loudly_without_gpu():
 def test_argument_errors_reported_before_touching_the_device():
     lib = _lib.load()
     h = ctypes.c_void_p()
-    for kw in (dict(pol=0), dict(theta_deg=10.0), dict(order=0), dict(order=200), dict(max_batch=0), dict(algo=2),
+    for kw in (dict(pol=2), dict(theta_deg=10.0), dict(order=0), dict(order=200), dict(max_batch=0), dict(algo=2),
                dict(precision=1)):
         base = dict(n_cells=256, order=40, n_inc=1.45, n_exit=1.0, n_groove=1.0, theta_deg=0.0, pol=1, max_batch=8,
                     device=0)

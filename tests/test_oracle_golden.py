@@ -88,3 +88,24 @@ def test_grad_golden_consistent_with_oracle_fd(golden_dir):
     np.testing.assert_allclose(got, g[n + "/fd_grad"][idx], rtol=2e-6, atol=2e-9)    # FD rounding noise ~ eps/h
     np.testing.assert_allclose(got, [-7.3443880e-04, 3.6901669e-03, -1.6564464e-03], rtol=2e-6)
     assert abs(O.efficiency(g[n + "/pattern"]) - float(g[n + "/eff"])) < 1e-12       # BLAS thread count changes the last digits
+
+
+def test_stack_restatement_matches_reference_fixtures(golden_dir):
+    """oracle.rcwa_oracle.solve_stack (multilayer, TE, 'TMM' and 'SMM') against the unmodified reference (fixtures written by
+    oracle/make_stack_golden.py); the reference's own SMM / TMM layer-order relation is part of what is pinned."""
+    import os
+    import numpy as np
+    from oracle import rcwa_oracle as O
+    g = np.load(os.path.join(golden_dir, "rcwa_stack_golden.npz"))
+    names = sorted({k.split("/")[0] for k in g.files})
+    assert len(names) == 10
+    for n in names:
+        r = O.evaluate_stack(g[n + "/structs"], float(g[n + "/wavelength"]), float(g[n + "/angle"]), int(g[n + "/order"]),
+                             g[n + "/thickness"], int(g[n + "/pol"]), str(g[n + "/algo"]))
+        assert abs(r.eff - float(g[n + "/ref_eff"])) <= 1e-12, n
+        assert np.abs(r.tran_cut - g[n + "/ref_tran_cut"]).max() <= 1e-12 and np.abs(r.refl_cut - g[n + "/ref_refl_cut"]).max() <= 1e-12
+    # the quirk itself: SMM(list) == TMM(reversed list) for a two-layer stack
+    s = g["ML2_block16_N20_TMM/structs"]; th = g["ML2_block16_N20_TMM/thickness"]
+    a = O.evaluate_stack(s, 1100.0, 60.0, 20, th, 1, 'SMM').eff
+    b = O.evaluate_stack(s[::-1], 1100.0, 60.0, 20, th[::-1], 1, 'TMM').eff
+    assert abs(a - b) <= 1e-11 and abs(a - float(g["ML2_block16_N20_SMM/ref_eff"])) <= 1e-12
