@@ -283,13 +283,23 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     // large orders (96 < ff <= 208): more sweeps per systolic pass and smaller row blocks -> more independent rotation chains
     // per SM (the 64-row / 2-sweep variant runs ONE 64-thread CTA per SM at ff = 201: profiles/r02k_ncu_full_c5_*.csv)
     if (ff > 96 && ff <= 208) {
-      int v = 2;      // measured at order 100, batch 512 (profiles/r02l_apply_variants.txt): 0: 8.25 ms, 1: 7.32, 2: 6.46, 3: 6.95
+      // measured at order 100, batch 512 (profiles/r02l_apply_variants.txt, r02p_apply_variants.txt): 0 (64 rows x 2 sweeps): 8.25 ms,
+      // 1 (32 x 4): 7.32, 2 (64 x 4): 6.46, 3 (32 x 2): 6.95, 4 (67 x 4: three row blocks cover ff = 201 exactly): 6.01, 5 (67 x 6): 4.92
+      int v = (ff > 134 && ff <= 201) ? 5 : 2;
       if (const char* e = getenv("PIRL_APPLY")) v = atoi(e);
       h->apply_variant = v;
       if (v == 1) { h->apply_rows = 32; h->apply_k = 4; h->apply_smem = apply_bytes(32, 4); CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 4, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<32, 4, 208>)); }
       else if (v == 2) { h->apply_rows = 64; h->apply_k = 4; h->apply_smem = apply_bytes(64, 4); CUDA_TRY(cudaFuncSetAttribute(k_apply<64, 4, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<64, 4, 208>)); }
       else if (v == 3) { h->apply_rows = 32; h->apply_k = 2; h->apply_smem = apply_bytes(32, 2); CUDA_TRY(cudaFuncSetAttribute(k_apply<32, 2, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<32, 2, 208>)); }
+      else if (v == 4) { h->apply_rows = 67; h->apply_k = 4; h->apply_smem = apply_bytes(67, 4); CUDA_TRY(cudaFuncSetAttribute(k_apply<67, 4, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<67, 4, 208>)); }
+      else if (v == 5) { h->apply_rows = 67; h->apply_k = 6; h->apply_smem = apply_bytes(67, 6); CUDA_TRY(cudaFuncSetAttribute(k_apply<67, 6, 208>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<67, 6, 208>)); }
       else h->apply_variant = 0;
+    }
+    if (ff <= 81) {      // experiment: more sweeps per pass at the headline size (PIRL_APPLY81 = 6 or 8)
+      int k81 = 0;
+      if (const char* e = getenv("PIRL_APPLY81")) k81 = atoi(e);
+      if (k81 == 6) { h->apply_variant = 16; h->apply_rows = 96; h->apply_k = 6; h->apply_smem = apply_bytes(96, 6); CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 6, 81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<96, 6, 81>)); }
+      if (k81 == 8) { h->apply_variant = 18; h->apply_rows = 96; h->apply_k = 8; h->apply_smem = apply_bytes(96, 8); CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 8, 81>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->apply_smem)); CUDA_TRY(max_carveout(k_apply<96, 8, 81>)); }
     }
     h->ql_smem = (size_t)2 * ff * 32 * 8;
     CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(h->smem_optin - 1024)));
@@ -475,6 +485,10 @@ static void launch_apply(pirl_handle* h, const KParams& P, cudaStream_t st) {
     if (h->apply_variant == 1) k_apply<32, 4, 208><<<g, 32, h->apply_smem, st>>>(P);
     else if (h->apply_variant == 2) k_apply<64, 4, 208><<<g, 64, h->apply_smem, st>>>(P);
     else if (h->apply_variant == 3) k_apply<32, 2, 208><<<g, 32, h->apply_smem, st>>>(P);
+    else if (h->apply_variant == 4) k_apply<67, 4, 208><<<g, 67, h->apply_smem, st>>>(P);
+    else if (h->apply_variant == 5) k_apply<67, 6, 208><<<g, 67, h->apply_smem, st>>>(P);
+    else if (h->apply_variant == 16) k_apply<96, 6, 81><<<g, 96, h->apply_smem, st>>>(P);
+    else if (h->apply_variant == 18) k_apply<96, 8, 81><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 96 && h->ff <= 81) k_apply<96, 4, 81><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 96) k_apply<96, 4, 96><<<g, 96, h->apply_smem, st>>>(P);
     else if (h->apply_rows == 64) k_apply<64, 2, 256><<<g, 64, h->apply_smem, st>>>(P);

@@ -396,16 +396,33 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
       ck_cluster_sync();
       // corner terms -Y^T D^-1 Y of the eliminated pivots (every CTA holds all pivot rows)
       int bad = 0;
+      double* rdt = sm + S::cb;            // reciprocals of the pivots (the published-column buffers are free now)
+      double* rdb = sm + S::cb + FE;
+      for (int k = tid; k < ne; k += NT) {
+        if (!(dt[k] > 0.0) || !(db[k] > 0.0)) bad = 1;
+        rdt[k] = 1.0 / dt[k]; rdb[k] = 1.0 / db[k];
+      }
+      __syncthreads();
       for (int idx = tid; idx < nhI * nhI + nxb * nxb; idx += NT) {
-        double s = 0.0;
+        double s0 = 0.0, s1 = 0.0;          // two chains: the sums run over ~200 pivots
         if (idx < nhI * nhI) {
           const int a = idx / nhI, b = idx - a * nhI;
-          for (int k = 0; k < ne; ++k) { if (!(dt[k] > 0.0)) bad = 1; s = fma(Yt[k * NHMAX + a] / dt[k], Yt[k * NHMAX + b], s); }
-          CTm[(np + a) * NCT + np + b] = -s;
+          int k = 0;
+          for (; k + 1 < ne; k += 2) {
+            s0 = fma(Yt[k * NHMAX + a] * rdt[k], Yt[k * NHMAX + b], s0);
+            s1 = fma(Yt[(k + 1) * NHMAX + a] * rdt[k + 1], Yt[(k + 1) * NHMAX + b], s1);
+          }
+          if (k < ne) s0 = fma(Yt[k * NHMAX + a] * rdt[k], Yt[k * NHMAX + b], s0);
+          CTm[(np + a) * NCT + np + b] = -(s0 + s1);
         } else {
           const int q = idx - nhI * nhI, a = q / nxb, b = q - a * nxb;
-          for (int k = 0; k < ne; ++k) { if (!(db[k] > 0.0)) bad = 1; s = fma(Yb[k * NXS + a] / db[k], Yb[k * NXS + b], s); }
-          CBm[(np + a) * NCB + np + b] = -s;
+          int k = 0;
+          for (; k + 1 < ne; k += 2) {
+            s0 = fma(Yb[k * NXS + a] * rdb[k], Yb[k * NXS + b], s0);
+            s1 = fma(Yb[(k + 1) * NXS + a] * rdb[k + 1], Yb[(k + 1) * NXS + b], s1);
+          }
+          if (k < ne) s0 = fma(Yb[k * NXS + a] * rdb[k], Yb[k * NXS + b], s0);
+          CBm[(np + a) * NCB + np + b] = -(s0 + s1);
         }
       }
       if (bad) cnt[5] = 1;       // a non-positive pivot: K was not positive definite

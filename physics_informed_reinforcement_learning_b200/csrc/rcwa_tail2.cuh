@@ -396,16 +396,33 @@ __global__ void __maxnreg__(C::MAXREG) rk_tail2(KParams P) {
     }
     __syncthreads();
     // corner terms -Y^T D^-1 Y of the eliminated pivots
+    double* rdt = cbuf;                    // reciprocals of the pivots (the published-column buffers are free now)
+    double* rdb = cbuf + FE;
+    for (int k = tid; k < ne; k += NT) {
+      if (!(dt[k] > 0.0) || !(db[k] > 0.0)) bad = 1;
+      rdt[k] = 1.0 / dt[k]; rdb[k] = 1.0 / db[k];
+    }
+    __syncthreads();
     for (int idx = tid; idx < nhI * nhI + nxb * nxb; idx += NT) {
-      double s = 0.0;
+      double s0 = 0.0, s1 = 0.0;            // two chains over the ~75 pivots
       if (idx < nhI * nhI) {
         const int a = idx / nhI, b = idx - a * nhI;
-        for (int k = 0; k < ne; ++k) { if (!(dt[k] > 0.0)) bad = 1; s = fma(Yt[k * NHMAX + a] / dt[k], Yt[k * NHMAX + b], s); }
-        CTm[(np + a) * NCT + np + b] = -s;
+        int k = 0;
+        for (; k + 1 < ne; k += 2) {
+          s0 = fma(Yt[k * NHMAX + a] * rdt[k], Yt[k * NHMAX + b], s0);
+          s1 = fma(Yt[(k + 1) * NHMAX + a] * rdt[k + 1], Yt[(k + 1) * NHMAX + b], s1);
+        }
+        if (k < ne) s0 = fma(Yt[k * NHMAX + a] * rdt[k], Yt[k * NHMAX + b], s0);
+        CTm[(np + a) * NCT + np + b] = -(s0 + s1);
       } else {
         const int q = idx - nhI * nhI, a = q / nxb, b = q - a * nxb;
-        for (int k = 0; k < ne; ++k) { if (!(db[k] > 0.0)) bad = 1; s = fma(Yb[k * NXB + a] / db[k], Yb[k * NXB + b], s); }
-        CBm[(np + a) * NCB + np + b] = -s;
+        int k = 0;
+        for (; k + 1 < ne; k += 2) {
+          s0 = fma(Yb[k * NXB + a] * rdb[k], Yb[k * NXB + b], s0);
+          s1 = fma(Yb[(k + 1) * NXB + a] * rdb[k + 1], Yb[(k + 1) * NXB + b], s1);
+        }
+        if (k < ne) s0 = fma(Yb[k * NXB + a] * rdb[k], Yb[k * NXB + b], s0);
+        CBm[(np + a) * NCB + np + b] = -(s0 + s1);
       }
     }
     if (bad) cnt[5] = 1;       // a non-positive pivot: K was not positive definite

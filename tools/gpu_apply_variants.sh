@@ -1,6 +1,6 @@
 #!/bin/bash
 # k_apply variants at order 100 (PIRL_APPLY = 0 old 64 rows x 2 sweeps, 1: 32x4, 2: 64x4, 3: 32x2): stage times at batch 512
-for v in 0 1 2 3; do
+for v in ${VARIANTS:-0 1 2 3 4 5}; do
   echo "PIRL_APPLY=$v"
   PIRL_APPLY=$v timeout 200 python - <<'P'
 import sys; sys.path.insert(0, ".")
