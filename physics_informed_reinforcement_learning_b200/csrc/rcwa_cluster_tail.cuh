@@ -7,7 +7,8 @@
 // along), leaving a complex border system of about 25 unknowns.  Replaces _base.py:159, transfer_method.py:42-75 and
 // solver.py:29-38 of the reference.
 // Cluster organisation (see rcwa_cluster.cuh): the tile is split by thread row; each elimination step all-gathers the pivot
-// column and broadcasts the pivot row of the extra columns through distributed shared memory (one barrier.cluster per step).
+// column and broadcasts the pivot row of the extra columns through distributed shared memory as one pipelined round
+// (st.async + mbarrier transaction count, look-ahead publish of the next column: CkPipe).
 // The parked blocks are written and read by the same thread row, so they stay in the owner's shared memory; the small
 // corner blocks are broadcast and every CTA solves the border system redundantly (CTA 0 stores the result).  W is streamed
 // from L2 in row chunks, permuted into sorted mode order while it is staged.
@@ -45,7 +46,8 @@ struct CTailSmem {
   static constexpr int parkSS = CB + pirl_even(NCB * NCB);     // [NSMAX][NSMAX]  (entries of this CTA's rows only)
   static constexpr int parkX = parkSS + NSMAX * NSMAX;         // [NSMAX][NPX]
   static constexpr int ints = parkX + pirl_even(NSMAX * NPX);  // pos[FE], ipos[FE], pI[8], pII[8], cnt[16] (ints)
-  static constexpr int chunk = pirl_even(ints + FE + 16);      // [RCH][WLD] staged rows of W; later the border system
+  static constexpr int mbar = pirl_even(ints + FE + 16);       // two mbarriers (CkPipe)
+  static constexpr int chunk = mbar + 2;                       // [RCH][WLD] staged rows of W; later the border system
   static constexpr int zsys = 2 * NBMAX * (NBMAX + 1);
   static constexpr int doubles = chunk + pirl_even((RCH * WLD > zsys) ? RCH * WLD : zsys);
 };
@@ -85,74 +87,138 @@ __device__ __forceinline__ void ck_product(double (&t)[C::RT][C::CT], const doub
   }
 }
 
-// LDL^T steps on pivots [kbeg, kend) of the symmetric cluster tile, carrying the extra columns x0 (column tj).  The pivot
-// column is all-gathered, the pivot row of the extra columns is broadcast by its owner CTA; every CTA keeps the pivot and
-// that row (Ys[k][0..NXS), ds[k]) for the corner term -Y^T D^-1 Y.
+// The same product on the FP64 tensor path (mma.sync.aligned.m8n8k4.f64; it wins in g_eigback,
+// profiles/r02m_dmma_trial_g_eigback.txt, but LOSES here -- see CK_PRODUCT below; kept as the measured alternative).  This CTA's rows of W^T D W form RT * ceil(TRL / 8) row tiles of 8 (each tile: eight
+// consecutive thread rows of one tile-row block a), the FF columns (FF + 7) / 8 column tiles; a warp owns up to CPW column
+// tiles for ALL row tiles, walks the staged harmonics four at a time (A fragment = d_r W[r][row], B fragment = W[r][col], one
+// double per lane each) and keeps its accumulators in registers over all chunks.  The result is brought into the cyclic
+// register-tile layout through the (then free) chunk buffer, two tile-row blocks at a time.
 template <class C, class S>
-__device__ __forceinline__ void ck_ldlt_range(double (&t)[C::RT][C::CT], double (&x0)[C::RT], int kbeg, int kend, double* sm,
-                                              const uint32_t (&rb)[C::NCTA], double* Ys, int ys, double* ds, int nx, bool act,
-                                              int ti, int tj, int tid) {
-  constexpr int TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, FE = C::FE, NCTA = C::NCTA, SCW = S::SCW, NXS = S::NXS;
-  auto bcast = [&](int off, double v) {
+__device__ __forceinline__ void ck_product_mma(double (&t)[C::RT][C::CT], const double* __restrict__ Wg, int FFR, const int* pos,
+                                               const double* dre, double* chunk, int crank, int til, int tj, int tid) {
+  constexpr int TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, NT = C::NT, TRL = C::TRL, FF = C::FF, WLD = S::WLD, RCH = S::RCH;
+  constexpr int TPA = (TRL + 7) / 8;                 // row tiles per tile-row block
+  constexpr int NRT = RT * TPA;                      // row tiles of this CTA
+  constexpr int NCT = (FF + 7) / 8;                  // column tiles
+  constexpr int NW = NT / 32;
+  constexpr int CPW = (NCT + NW - 1) / NW;           // column tiles per warp
+  static_assert(2 * TRL * WLD <= RCH * WLD, "the staging of two tile-row blocks must fit the chunk buffer");
+  const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t4 = lane & 3;
+  double acc[CPW][NRT][2];
+  int arow[NRT];                                     // sorted-mode index of this lane's row in each row tile (-1: padding)
+  int bcol[CPW];                                     // column of this lane in each of its column tiles (-1: none)
 #pragma unroll
-    for (int r = 0; r < NCTA; ++r) ck_st_cluster(rb[r] + 8u * (uint32_t)off, v);
-  };
-  bool done = false;
-#pragma unroll
-  for (int kb = 0; kb < CT; ++kb) {
-    const int ka = kb / C::KA_PER_KB;
-    if ((kb + 1) * TC <= kbeg) continue;          // uniform
-#pragma unroll 1
-    for (int kj = 0; kj < TC; ++kj) {
-      const int k = kb * TC + kj;
-      if (k < kbeg) continue;
-      if (k >= kend) { done = true; break; }
-      const int kti = k - ka * TR;
-      const int cbo = S::cb + (k & 1) * FE, sco = S::sc + (k & 1) * SCW;
-      if (act) {
-        if (tj == kj) {
-#pragma unroll
-          for (int a = 0; a < RT; ++a) if (a >= ka) { const int i = ti + TR * a; bcast(cbo + i, (i > k) ? t[a][kb] : 0.0); }
-          if (ti == kti) { const double d = t[ka][kb]; bcast(sco + NXS, 1.0 / d); bcast(sco + NXS + 1, d); }
-        }
-        if (ti == kti) bcast(sco + tj, x0[ka]);
-      }
-      ck_cluster_sync();
-      const double* cb = sm + cbo;
-      const double* sc = sm + sco;
-      const double pinv = sc[NXS];
-      if (tid < nx) Ys[k * ys + tid] = sc[tid];
-      if (tid == 32) ds[k] = sc[NXS + 1];
-      double l[RT];
-#pragma unroll
-      for (int a = 0; a < RT; ++a) if (a >= ka) l[a] = cb[ti + TR * a] * pinv;
-      const double y0 = sc[tj];
-#pragma unroll
-      for (int a = 0; a < RT; ++a) if (a >= ka) x0[a] = fma(-l[a], y0, x0[a]);
-#pragma unroll
-      for (int b = 0; b < CT; ++b)
-        if (b >= kb) {
-          const double r = cb[tj + TC * b];
-#pragma unroll
-          for (int a = 0; a < RT; ++a) if (a >= ka) t[a][b] = fma(-l[a], r, t[a][b]);
-        }
-    }
-    if (done) break;
+  for (int rt = 0; rt < NRT; ++rt) {
+    const int a = rt / TPA, tl = (rt % TPA) * 8 + g;
+    arow[rt] = (tl < TRL) ? crank * TRL + tl + TR * a : -1;
   }
+#pragma unroll
+  for (int c = 0; c < CPW; ++c) {
+    const int ct = warp + NW * c, j = ct * 8 + g;
+    bcol[c] = (ct < NCT && j < FF) ? j : -1;
+#pragma unroll
+    for (int rt = 0; rt < NRT; ++rt) { acc[c][rt][0] = 0.0; acc[c][rt][1] = 0.0; }
+  }
+  for (int r0 = 0; r0 < FFR; r0 += RCH) {
+    const int nr = min(RCH, FFR - r0);
+    __syncthreads();
+    for (int idx = tid; idx < nr * FFR; idx += NT) {
+      const int rr = idx / FFR, j = idx - rr * FFR;
+      chunk[rr * WLD + pos[j]] = __ldg(&Wg[(size_t)(r0 + rr) * FFR + j]);
+    }
+    for (int idx = tid; idx < nr * (FF - FFR); idx += NT) {      // padded (dummy) modes sort first: zero columns of W
+      const int rr = idx / (FF - FFR), j = idx - rr * (FF - FFR);
+      chunk[rr * WLD + j] = 0.0;
+    }
+    __syncthreads();
+    for (int k0 = 0; k0 < nr; k0 += 4) {
+      const int r = k0 + t4;
+      const bool rok = r < nr;
+      const double d = rok ? dre[r0 + r] : 0.0;      // propagating harmonics have d = 0: they drop out
+      const double* wrow = chunk + (rok ? r : 0) * WLD;
+      double af[NRT], bf[CPW];
+#pragma unroll
+      for (int rt = 0; rt < NRT; ++rt) af[rt] = (arow[rt] >= 0) ? d * wrow[arow[rt]] : 0.0;
+#pragma unroll
+      for (int c = 0; c < CPW; ++c) bf[c] = (bcol[c] >= 0 && rok) ? wrow[bcol[c]] : 0.0;
+#pragma unroll
+      for (int c = 0; c < CPW; ++c) {
+        if (warp + NW * c >= NCT) continue;          // uniform per warp
+#pragma unroll
+        for (int rt = 0; rt < NRT; ++rt)
+          asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                       : "+d"(acc[c][rt][0]), "+d"(acc[c][rt][1])
+                       : "d"(af[rt]), "d"(bf[c]));
+      }
+    }
+  }
+  // accumulators (C[row = g][col = 2 t4 + {0, 1}] of every tile) -> cyclic register tile, two tile-row blocks at a time
+#pragma unroll
+  for (int h = 0; h < (RT + 1) / 2; ++h) {
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < CPW; ++c) {
+      const int ct = warp + NW * c;
+      if (ct >= NCT) continue;
+#pragma unroll
+      for (int rt = 0; rt < NRT; ++rt) {
+        const int a = rt / TPA, tl = (rt % TPA) * 8 + g;
+        if (a / 2 != h || tl >= TRL) continue;
+        double* dst = chunk + ((a & 1) * TRL + tl) * WLD + ct * 8 + 2 * t4;
+        if (ct * 8 + 2 * t4 < FF) dst[0] = acc[c][rt][0];
+        if (ct * 8 + 2 * t4 + 1 < FF) dst[1] = acc[c][rt][1];
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int a = 0; a < RT; ++a)
+      if (a / 2 == h) {
+#pragma unroll
+        for (int b = 0; b < CT; ++b) t[a][b] = chunk[((a & 1) * TRL + til) * WLD + tj + TC * b];
+      }
+  }
+  __syncthreads();       // the chunk buffer is free again (padded sorted columns are re-zeroed by the caller's next structure)
 }
 
-// Symmetric sweep steps on pivots [kbeg, kend) inside the window rows / columns >= kbeg:  afterwards
-//   t[S,S] = -(Schur_S)^-1,  t[S,R] = (Schur_S)^-1 M_SR,  t[R,R] = Schur complement,  x0[S] = (Schur_S)^-1 x_S,  x0[R] = Schur.
-template <class C, class S>
-__device__ __forceinline__ void ck_sweep_range(double (&t)[C::RT][C::CT], double (&x0)[C::RT], int kbeg, int kend, double* sm,
-                                               const uint32_t (&rb)[C::NCTA], double* Ys, int ys, double* ds, int nx, bool act,
-                                               int ti, int tj, int tid) {
-  constexpr int TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, FE = C::FE, NCTA = C::NCTA, SCW = S::SCW, NXS = S::NXS;
-  auto bcast = [&](int off, double v) {
+// Elimination steps on pivots [kbeg, kend) of the symmetric cluster tile, carrying the extra columns x0 (column tj), as
+// PIPELINED ROUNDS (CkPipe, rcwa_cluster.cuh): per step one all-gather of the pivot column (every CTA), the pivot row of the
+// extra columns and 1/d, d (owner CTA), stored with st.async and counted on an mbarrier; the owners of column k + 1 and of
+// row k + 1 apply step k to their entries FIRST and send round k + 1 before the bulk of step k is applied.
+//   SWEEP = false: LDL^T steps (rows / columns > k);
+//   SWEEP = true : symmetric sweep steps inside the window rows / columns >= kbeg; afterwards
+//     t[S,S] = -(Schur_S)^-1,  t[S,R] = (Schur_S)^-1 M_SR,  t[R,R] = Schur complement,  x0[S] = (Schur_S)^-1 x_S,  x0[R] = Schur.
+// Every CTA keeps the pivot and the pivot row of the extra columns (Ys[k][0..nx), ds[k]) for the corner term -Y^T D^-1 Y.
+template <class C, class S, bool SWEEP>
+__device__ __forceinline__ void ck_elim_range(double (&t)[C::RT][C::CT], double (&x0)[C::RT], int kbeg, int kend, double* sm,
+                                              CkPipe<C::NCTA>& pipe, double* Ys, int ys, double* ds, int nx, bool act, int ti,
+                                              int tj, int tid) {
+  constexpr int TR = C::TR, TC = C::TC, RT = C::RT, CT = C::CT, FE = C::FE, SCW = S::SCW, NXS = S::NXS;
+  if (kbeg >= kend) return;
+  const int a0 = SWEEP ? kbeg / TR : 0, b0 = SWEEP ? kbeg / TC : 0;     // sweep: first tile blocks that intersect the window
+  // publish round KK: column KK (tile column KBC) by its owners, 1/d and d by the pivot owner, x0 of row KK by the row owners
+#define CK_ELIM_PUBLISH_COL(KBC, KK)                                                                               \
+  do {                                                                                                             \
+    const int kac_ = (KBC) / C::KA_PER_KB;                                                                         \
+    const int cbo_ = S::cb + ((KK) & 1) * FE, sco_ = S::sc + ((KK) & 1) * SCW;                                     \
+    _Pragma("unroll") for (int a = 0; a < RT; ++a) {                                                               \
+      const int i_ = ti + TR * a;                                                                                  \
+      if (SWEEP) { if (a >= a0) pipe.pub(cbo_ + i_, (i_ >= kbeg) ? ((i_ == (KK)) ? t[a][KBC] - 1.0 : t[a][KBC]) : 0.0); } \
+      else if (a >= kac_) pipe.pub(cbo_ + i_, (i_ > (KK)) ? t[a][KBC] : 0.0);                                      \
+    }                                                                                                              \
+    if (ti == (KK) - kac_ * TR) { const double d_ = t[kac_][KBC]; pipe.pub(sco_ + NXS, 1.0 / d_); pipe.pub(sco_ + NXS + 1, d_); } \
+  } while (0)
+#define CK_ELIM_PUBLISH_ROW(KAR, KK) pipe.pub(S::sc + ((KK) & 1) * SCW + tj, x0[KAR])
+  // prologue: round kbeg (every thread of this CTA is past a CTA barrier that follows its reads of the previous round)
+  if (act) {
 #pragma unroll
-    for (int r = 0; r < NCTA; ++r) ck_st_cluster(rb[r] + 8u * (uint32_t)off, v);
-  };
-  const int a0 = kbeg / TR, b0 = kbeg / TC;     // first tile row / column blocks that intersect the window
+    for (int kb = 0; kb < CT; ++kb) {
+      const int ka = kb / C::KA_PER_KB;
+      if (kbeg >= kb * TC && kbeg < (kb + 1) * TC) {
+        if (tj == kbeg - kb * TC) CK_ELIM_PUBLISH_COL(kb, kbeg);
+        if (ti == kbeg - ka * TR) CK_ELIM_PUBLISH_ROW(ka, kbeg);
+      }
+    }
+  }
   bool done = false;
 #pragma unroll
   for (int kb = 0; kb < CT; ++kb) {
@@ -164,42 +230,65 @@ __device__ __forceinline__ void ck_sweep_range(double (&t)[C::RT][C::CT], double
       if (k < kbeg) continue;
       if (k >= kend) { done = true; break; }
       const int kti = k - ka * TR;
-      const int cbo = S::cb + (k & 1) * FE, sco = S::sc + (k & 1) * SCW;
-      // published column: zeros on finished rows, d - 1 at the pivot (u_k = -(d - 1) p = p - 1 and v_k = d - 1 then need no
-      // special case on the reader side); the pivot owner also publishes 1/d
-      if (act) {
-        if (tj == kj) {
-#pragma unroll
-          for (int a = 0; a < RT; ++a)
-            if (a >= a0) { const int i = ti + TR * a; bcast(cbo + i, (i >= kbeg) ? ((i == k) ? t[a][kb] - 1.0 : t[a][kb]) : 0.0); }
-          if (ti == kti) { const double d = t[ka][kb]; bcast(sco + NXS, 1.0 / d); bcast(sco + NXS + 1, d); }
-        }
-        if (ti == kti) bcast(sco + tj, x0[ka]);
-      }
-      ck_cluster_sync();
-      const double* cb = sm + cbo;
-      const double* sc = sm + sco;
+      pipe.wait(8u * (uint32_t)((SWEEP ? (RT - a0) : (RT - ka)) * TR + 2 + TC), tid);
+      const double* cb = sm + S::cb + (k & 1) * FE;
+      const double* sc = sm + S::sc + (k & 1) * SCW;
       const double p = sc[NXS];
       if (tid < nx) Ys[k * ys + tid] = sc[tid];
       if (tid == 32) ds[k] = sc[NXS + 1];
-      double u[RT];
+      double u[RT], v[CT];
 #pragma unroll
-      for (int a = 0; a < RT; ++a) if (a >= a0) u[a] = -cb[ti + TR * a] * p;
+      for (int a = 0; a < RT; ++a) if (a >= (SWEEP ? a0 : ka)) u[a] = -cb[ti + TR * a] * p;
+#pragma unroll
+      for (int b = 0; b < CT; ++b) if (b >= (SWEEP ? b0 : kb)) v[b] = cb[tj + TC * b];
       const double y0 = sc[tj];
+      __syncthreads();       // round k consumed by every thread of this CTA: the next round may be sent
 #pragma unroll
-      for (int a = 0; a < RT; ++a) if (a >= a0) x0[a] = fma(u[a], y0, x0[a]);
+      for (int a = 0; a < RT; ++a) if (a >= (SWEEP ? a0 : ka)) x0[a] = fma(u[a], y0, x0[a]);
+      if (k + 1 < kend && act) {       // look-ahead: column k + 1 and the extra-column entries of row k + 1 first
+        const int kbn = (kj + 1 < TC) ? kb : ((kb + 1 < CT) ? kb + 1 : kb);     // constant per branch after unrolling
+        const int kan = kbn / C::KA_PER_KB;
+        if (kj + 1 < TC) {
+          if (tj == kj + 1) {
+#pragma unroll
+            for (int a = 0; a < RT; ++a) if (a >= (SWEEP ? a0 : ka)) t[a][kb] = fma(u[a], v[kb], t[a][kb]);
+            v[kb] = 0.0;
+            CK_ELIM_PUBLISH_COL(kb, k + 1);
+          }
+          if (ti == k + 1 - ka * TR) CK_ELIM_PUBLISH_ROW(ka, k + 1);
+        } else if (kb + 1 < CT) {
+          if (tj == 0) {
+#pragma unroll
+            for (int a = 0; a < RT; ++a)
+              if (a >= (SWEEP ? a0 : ka)) t[a][(kb + 1 < CT) ? kb + 1 : kb] = fma(u[a], v[(kb + 1 < CT) ? kb + 1 : kb], t[a][(kb + 1 < CT) ? kb + 1 : kb]);
+            v[(kb + 1 < CT) ? kb + 1 : kb] = 0.0;
+            CK_ELIM_PUBLISH_COL(((kb + 1 < CT) ? kb + 1 : kb), k + 1);
+          }
+          if (ti == k + 1 - kan * TR) CK_ELIM_PUBLISH_ROW((((kb + 1 < CT) ? kb + 1 : kb) / C::KA_PER_KB), k + 1);
+        }
+      }
 #pragma unroll
       for (int b = 0; b < CT; ++b)
-        if (b >= b0) {
-          const double v = cb[tj + TC * b];
+        if (b >= (SWEEP ? b0 : kb)) {
 #pragma unroll
-          for (int a = 0; a < RT; ++a) if (a >= a0) t[a][b] = fma(u[a], v, t[a][b]);
+          for (int a = 0; a < RT; ++a) if (a >= (SWEEP ? a0 : ka)) t[a][b] = fma(u[a], v[b], t[a][b]);
         }
-      if (ti == kti && tj == kj) t[ka][kb] = -p;
+      if (SWEEP && ti == kti && tj == kj) t[ka][kb] = -p;
     }
     if (done) break;
   }
+#undef CK_ELIM_PUBLISH_COL
+#undef CK_ELIM_PUBLISH_ROW
 }
+
+// measured at order 100 (profiles/r02u_cluster_check_dmma_products.txt): the DMMA product costs 208k / 145k clocks per
+// structure against 131k / 113k for the register-tiled DFMA product (4-way bank conflicts on the fragment loads at the odd
+// row stride, 2.75 warps per scheduler) -> DFMA stays the default; -DPIRL_CK_PRODUCT_MMA builds the tensor variant
+#ifdef PIRL_CK_PRODUCT_MMA
+#define CK_PRODUCT(t_, W_, F_, p_, d_, c_) ck_product_mma<C, S>(t_, W_, F_, p_, d_, c_, crank, til, tj, tid)
+#else
+#define CK_PRODUCT(t_, W_, F_, p_, d_, c_) ck_product<C, S>(t_, W_, F_, p_, d_, c_, ti, tj, tid)
+#endif
 
 template <class C, int NSMAX, int NPMAX, int NHMAX, int RCH>
 __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
@@ -238,13 +327,9 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
   const int til = act ? tid / TC : TRL - 1;
   const int tj = act ? tid % TC : TC - 1;
   const int ti = crank * TRL + til;
-  uint32_t rb[NCTA];
-#pragma unroll
-  for (int r = 0; r < NCTA; ++r) rb[r] = ck_mapa(ck_smem_u32(sm), (uint32_t)r);
-  auto bcast = [&](int off, double v) {
-#pragma unroll
-    for (int r = 0; r < NCTA; ++r) ck_st_cluster(rb[r] + 8u * (uint32_t)off, v);
-  };
+  CkPipe<NCTA> pipe;
+  pipe.init(sm, S::mbar, tid);
+  auto bcast = [&](int off, double v) { pipe.bcast(off, v); };
   const uint32_t ints_b = 8u * (uint32_t)S::ints + 4u * (uint32_t)(2 * FE + 16);     // byte offset of cnt[]
   ck_cluster_sync();
 
@@ -318,7 +403,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
       // sorted mode i -> column of W in global memory (-1: padded dummy mode)
       auto wglob = [&](int harm, int i) -> double { return (i >= npad) ? __ldg(&Wg[(size_t)harm * FFR + ipos[i]]) : 0.0; };
       // =========================== top: R_I + C, eliminate I (LDL^T), sweep S ===========================
-      ck_product<C, S>(t, Wg, FFR, pos, dre, chunk, ti, tj, tid);
+      CK_PRODUCT(t, Wg, FFR, pos, dre, chunk);
 #pragma unroll
       for (int a = 0; a < RT; ++a) {
         const int i = ti + TR * a;
@@ -327,9 +412,9 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
         x0[a] = (tj < nhI) ? wglob(pI[tj], i) : 0.0;
       }
       CK_PHASE(9);
-      ck_ldlt_range<C, S>(t, x0, 0, ni, sm, rb, Yt, NHMAX, dt, nhI, act, ti, tj, tid);
+      ck_elim_range<C, S, false>(t, x0, 0, ni, sm, pipe, Yt, NHMAX, dt, nhI, act, ti, tj, tid);
       CK_PHASE(10);
-      ck_sweep_range<C, S>(t, x0, ni, ne, sm, rb, Yt, NHMAX, dt, nhI, act, ti, tj, tid);
+      ck_elim_range<C, S, true>(t, x0, ni, ne, sm, pipe, Yt, NHMAX, dt, nhI, act, ti, tj, tid);
       CK_PHASE(11);
       // ---- park (this CTA's rows only): Sg (Schur_S)^-1 Sg, Sg G_P, Sg G_w; top corner blocks -> every CTA ----
       if (act) {
@@ -355,7 +440,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
       }
       ck_cluster_sync();    // every CTA has left the top sweep before the bottom eliminations reuse the published buffers
       // =========================== bottom: R_II + C, eliminate I, fold the top in, eliminate S ===========================
-      ck_product<C, S>(t, Wg, FFR, pos, dre + FE, chunk, ti, tj, tid);
+      CK_PRODUCT(t, Wg, FFR, pos, dre + FE, chunk);
 #pragma unroll
       for (int a = 0; a < RT; ++a) {
         const int i = ti + TR * a;
@@ -364,7 +449,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
         x0[a] = (tj < nhII) ? wglob(pII[tj], i) : 0.0;
       }
       CK_PHASE(12);
-      ck_ldlt_range<C, S>(t, x0, 0, ni, sm, rb, Yb, NXS, db, nxb, act, ti, tj, tid);
+      ck_elim_range<C, S, false>(t, x0, 0, ni, sm, pipe, Yb, NXS, db, nxb, act, ti, tj, tid);
       __syncthreads();      // parked blocks of this CTA are visible
       if (act) {
 #pragma unroll
@@ -378,7 +463,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
           }
         }
       }
-      ck_ldlt_range<C, S>(t, x0, ni, ne, sm, rb, Yb, NXS, db, nxb, act, ti, tj, tid);
+      ck_elim_range<C, S, false>(t, x0, ni, ne, sm, pipe, Yb, NXS, db, nxb, act, ti, tj, tid);
       CK_PHASE(13);
       // ---- bottom corner blocks -> every CTA ----
       if (act) {
@@ -566,7 +651,7 @@ __global__ void __launch_bounds__(C::NT, 1) ck_tail2(KParams P) {
     if (crank == 0 && tid == 0) {
       const int nxt = P.queue ? nclusters + atomicAdd(P.queue, 1) : sidx + nclusters;
 #pragma unroll
-      for (int r = 0; r < NCTA; ++r) ck_st_cluster_i32(rb[r] + ints_b + 4u * 8u, nxt);
+      for (int r = 0; r < NCTA; ++r) ck_st_cluster_i32(pipe.rb[r] + ints_b + 4u * 8u, nxt);
     }
     ck_cluster_sync();
     sidx = cnt[8];
