@@ -79,7 +79,8 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for src in SOURCES:
         if force or _unit_stale(src):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas=-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", _obj(src)]
+            extra = os.environ.get("PIRL_NVCC_EXTRA", "").split()      # e.g. -DPIRL_CK_PRODUCT_MMA (experiments)
+            cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas=-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", _obj(src)]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)))
     for src, p in procs:       # the units compile in parallel
         out, err = p.communicate()

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Per-source-line warp-stall samples of one kernel: joins `ncu --page source` (SASS, sampled) with `nvdisasm --print-line-info`.
 
-    python tools/ncu_lines.py <rep.ncu-rep> <kernel-substring> [lib.so] [top]
+    python tools/ncu_lines.py <rep.ncu-rep> <kernel-substring> [lib.so] [top] [mangled-substring]
 """
 import collections
 import csv
@@ -14,16 +14,19 @@ import tempfile
 rep, kern = sys.argv[1], sys.argv[2]
 lib = sys.argv[3] if len(sys.argv) > 3 else "physics_informed_reinforcement_learning_b200/libpirl_rcwa.so"
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+sect = sys.argv[5] if len(sys.argv) > 5 else kern      # substring of the MANGLED name when several instances exist
 
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, capture_output=True)
-cubin = [os.path.join(tmp, f) for f in os.listdir(tmp) if f.endswith(".cubin")][0]
-dis = subprocess.run(["nvdisasm", "--print-line-info", cubin], capture_output=True, text=True).stdout
+dis = ""          # the library holds one cubin per translation unit
+for f in sorted(os.listdir(tmp)):
+    if f.endswith(".cubin"):
+        dis += subprocess.run(["nvdisasm", "--print-line-info", os.path.join(tmp, f)], capture_output=True, text=True).stdout
 # offset -> line for the wanted function
 off2line, cur, infn = {}, None, False
 for ln in dis.splitlines():
     if ln.startswith("\t.section\t.text."):
-        infn = kern in ln
+        infn = sect in ln
     if not infn:
         continue
     m = re.search(r'//## File ".*?([^/"]+)", line (\d+)', ln)
