@@ -88,8 +88,9 @@ __device__ __forceinline__ void ck_product(double (&t)[C::RT][C::CT], const doub
 }
 
 // The same product on the FP64 tensor path (mma.sync.aligned.m8n8k4.f64; it wins in g_eigback,
-// profiles/r02m_dmma_trial_g_eigback.txt, but LOSES here -- see CK_PRODUCT below; kept as the measured alternative).  This CTA's rows of W^T D W form RT * ceil(TRL / 8) row tiles of 8 (each tile: eight
-// consecutive thread rows of one tile-row block a), the FF columns (FF + 7) / 8 column tiles; a warp owns up to CPW column
+// profiles/r02m_dmma_trial_g_eigback.txt, but LOSES here -- see CK_PRODUCT below; kept as the measured alternative).
+// This CTA's rows of W^T D W form RT * ceil(TRL / 8) row tiles of 8 (each tile: eight consecutive thread rows of one
+// tile-row block a), the FF columns (FF + 7) / 8 column tiles; a warp owns up to CPW column
 // tiles for ALL row tiles, walks the staged harmonics four at a time (A fragment = d_r W[r][row], B fragment = W[r][col], one
 // double per lane each) and keeps its accumulators in registers over all chunks.  The result is brought into the cyclic
 // register-tile layout through the (then free) chunk buffer, two tile-row blocks at a time.
