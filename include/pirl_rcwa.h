@@ -82,6 +82,35 @@ int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const double* params,
 int pirl_rcwa_eval_host(pirl_handle* h, const int8_t* patterns, const double* params, int32_t param_stride,
                         int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status);
 
+/* Forward evaluation for callers that cannot allocate device memory.  (No counterpart in the reference: its solver is NumPy
+ * on the host.  Added for deployments of THIS library.)
+ *
+ * Who needs it: a rollout worker sharing its GPU with a learner whose framework has already taken (almost) all device memory
+ * into its own pool -- XLA-style preallocation, a torch process with a memory fraction, an MPS client with a memory limit --
+ * where the cudaMallocs of pirl_rcwa_create fail; and loops that cannot tolerate the device-wide synchronisation a
+ * cudaMalloc / cudaFree implies.  This call takes NO handle and performs no cudaMalloc, cudaFree or other allocating call:
+ * every workspace lives in one static device array inside the library (about 18 MB, reserved on every GPU that loads the
+ * library, from module load until the process exits).
+ *
+ * Limits (anything beyond them is rejected with -13 and a message in pirl_last_error; use a handle instead):
+ *   cfg->order == PIRL_STATIC_ORDER, pol 1 (TM), algo 0, theta_deg 0, precision 0; 2 <= cfg->n_cells <= PIRL_STATIC_MAX_CELLS;
+ *   0 <= B <= PIRL_STATIC_MAX_BATCH structures per call (split larger batches into consecutive calls on one stream).
+ *   cfg->max_batch is ignored; cfg->device selects the GPU (made current, like the other entry points).
+ * Arguments and results as pirl_rcwa_eval (device pointers, work enqueued on `stream`); same kernels as a handle runs at
+ * order 40, so results agree with pirl_rcwa_eval to rounding.
+ *
+ * Set-up: the FIRST call on each device looks up the array's device address and sets kernel attributes; a call with a new
+ * n_cells re-uploads two small tables with cudaMemcpyAsync on `stream`.  Make the first call (per device, per n_cells) outside
+ * any stream capture.
+ * Sharing: all calls on a device use the same array and it keeps the previous call's contents; the call clears the counters
+ * that must start at zero itself.  Two calls that overlap on the GPU (different streams, or different host threads' streams)
+ * race on the array: issue them on one stream, or order the streams with events.  Host-side the call is serialised by a mutex. */
+#define PIRL_STATIC_ORDER 40
+#define PIRL_STATIC_MAX_CELLS 1024
+#define PIRL_STATIC_MAX_BATCH 32
+int pirl_rcwa_eval_static(const pirl_cfg* cfg, const int8_t* patterns, const double* params, int32_t param_stride,
+                          int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status, void* stream);
+
 /* Batched efficiency + adjoint gradient d eff / d s_p (p = 0..n_cells-1), s_p the cell value of solver.py:21-22
  * (u = (s+1)/2, eps = u (n_r^2 - n_g^2) + n_g^2, 1/eps taken cell by cell before convolution_matrix.py:89-114).
  * The reference has no gradient code; the contract is the central finite difference of its forward solver

@@ -11,7 +11,7 @@ SYMBOLS = [
     "pirl_rcwa_eval_host", "pirl_env_flip", "pirl_env_reward", "pirl_rcwa_launch_count", "pirl_rcwa_debug_fetch",
     "pirl_rcwa_num_stages", "pirl_rcwa_stage_name", "pirl_rcwa_set_stage_timing", "pirl_rcwa_stage_times",
     "pirl_rcwa_eval_grad", "pirl_rcwa_eval_grad_host", "pirl_rcwa_set_subchunk", "pirl_rcwa_eval_stack",
-    "pirl_rcwa_eval_stack_host",
+    "pirl_rcwa_eval_stack_host", "pirl_rcwa_eval_static",
 ]
 
 
@@ -44,6 +44,7 @@ def load():
     lib.pirl_rcwa_destroy.argtypes = [vp]
     lib.pirl_rcwa_eval.argtypes = [vp, dp, dp, i32, i64, dp, dp, dp, dp, vp]
     lib.pirl_rcwa_eval_host.argtypes = [vp, dp, dp, i32, i64, dp, dp, dp, dp]
+    lib.pirl_rcwa_eval_static.argtypes = [C.POINTER(PirlCfg), dp, dp, i32, i64, dp, dp, dp, dp, vp]
     lib.pirl_rcwa_eval_grad.argtypes = [vp, dp, dp, i32, i64, dp, dp, dp, vp]
     lib.pirl_rcwa_eval_grad_host.argtypes = [vp, dp, dp, i32, i64, dp, dp, dp]
     lib.pirl_rcwa_eval_stack.argtypes = [vp, dp, dp, i32, dp, i32, i32, i64, dp, dp, dp, dp, vp]
@@ -62,7 +63,7 @@ def load():
     lib.pirl_rcwa_stage_times.argtypes = [vp, dp, dp]
     for name in ("pirl_rcwa_create", "pirl_rcwa_destroy", "pirl_rcwa_eval", "pirl_rcwa_eval_host", "pirl_env_flip",
                  "pirl_env_reward", "pirl_rcwa_debug_fetch", "pirl_rcwa_set_stage_timing", "pirl_rcwa_stage_times", "pirl_rcwa_eval_grad",
-                 "pirl_rcwa_eval_grad_host", "pirl_rcwa_eval_stack", "pirl_rcwa_eval_stack_host"):
+                 "pirl_rcwa_eval_grad_host", "pirl_rcwa_eval_stack", "pirl_rcwa_eval_stack_host", "pirl_rcwa_eval_static"):
         getattr(lib, name).restype = C.c_int
     _lib = lib
     return lib

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -1010,4 +1011,175 @@ extern "C" int pirl_rcwa_eval_grad_host(pirl_handle* h, const int8_t* patterns, 
   if (status) CUDA_TRY(cudaMemcpyAsync(status, h->hd_status, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// pirl_rcwa_eval_static: the forward evaluation for callers that must not allocate device memory.
+//
+// Who that is: an RL rollout worker that shares its GPU with a learner whose framework has already claimed (nearly) all of the
+// device memory for its own pool (XLA-style preallocation, a torch process with a per-process memory fraction, an MPS client
+// with a memory limit), and any loop that cannot afford the device-wide synchronisation a cudaMalloc / cudaFree implies.  For
+// them pirl_rcwa_create -- a dozen cudaMallocs, gigabytes at large max_batch -- either fails or stalls the neighbour.
+//
+// This entry point takes no handle.  The workspaces that pirl_rcwa_create would cudaMalloc (the matrices handed from rk_front
+// to k_ql, k_apply and rk_tail2, the rotation stream, the twiddle tables, the k_tail spill area, the work counters) live in
+// ONE file-scope device array below, so the driver reserves them when the library's module is loaded and nothing is allocated
+// afterwards.  The price is a fixed, small shape: the DeflectorGym setting only (TM, order 40, at most PIRL_STATIC_MAX_CELLS
+// cells, at most PIRL_STATIC_MAX_BATCH structures per call), and about 18 MB held on every GPU that loads the library.
+//
+// The kernels are the ones pirl_rcwa_eval launches at order 40 (rk_front, k_ql, k_apply, rk_tail2, k_tail on the flagged
+// structures), all on the caller's stream, no side streams and no events.
+// ---------------------------------------------------------------------------------------------------
+namespace pirl_static {
+constexpr int kOrder = 40, kFF = 2 * kOrder + 1, kMaxB = 32, kMaxCells = 1024, kTailCtas = 8;
+static_assert(kFF == Cfg81::FF, "the static entry point runs the order-40 register-tile kernels");
+constexpr size_t al(size_t x) { return (x + 255) / 256 * 256; }
+constexpr size_t kM2 = (size_t)kFF * kFF, kMaxRot = 3 * kM2, kMaxSw = 16 * kFF;
+constexpr size_t kSpillStride = 2 * kM2 + 2 * (2 * kM2) + 16;            // doubles per k_tail CTA, as in pirl_rcwa_create
+// byte offsets into the array (every region starts on a 256-byte boundary)
+constexpr size_t oTw = 0;
+constexpr size_t oDk = oTw + al(kMaxCells * sizeof(cplx));
+constexpr size_t oC = oDk + al(kFF * sizeof(cplx));
+constexpr size_t oL = oC + al(kMaxB * kM2 * 8);
+constexpr size_t oW = oL + al(kMaxB * kM2 * 8);
+constexpr size_t oTri = oW + al(kMaxB * kM2 * 8);
+constexpr size_t oLam = oTri + al(kMaxB * 2 * kFF * 8);
+constexpr size_t oRot = oLam + al(kMaxB * kFF * 8);
+constexpr size_t oSw = oRot + al(kMaxB * kMaxRot * sizeof(cplx));
+constexpr size_t oSpill = oSw + al(kMaxB * kMaxSw * sizeof(uint16_t));
+constexpr size_t oCnt = oSpill + al(kTailCtas * kSpillStride * 8);      // nrot | nsw | wstatus | work counters: cleared per call
+constexpr size_t kCntBytes = al((3 * kMaxB + pirl_handle::kQueues) * sizeof(int));
+constexpr size_t kBytes = oCnt + kCntBytes;
+static_assert(kBytes < (size_t)20 << 20, "static workspace is meant to stay modest (< 20 MB)");
+}  // namespace pirl_static
+
+// The workspace itself.  HOST code must never pass this name to a kernel or a memcpy as if it were a pointer: on the host the
+// symbol is only a stand-in the runtime uses to look the array up; its device address comes from cudaGetSymbolAddress, taken
+// once per device in static_device() below.
+static __device__ __align__(256) unsigned char g_pirl_static_ws[pirl_static::kBytes];
+
+namespace pirl_static {
+struct Dev {
+  bool ready = false;
+  unsigned char* base = nullptr;   // device address of g_pirl_static_ws on this device
+  int tab_cells = 0;               // n_cells the twiddle / Dirichlet tables currently hold (0: none)
+  std::vector<cplx> tw, Dk;        // host copies of the tables (kept alive across the asynchronous upload)
+  pirl_handle h;                   // launch plan only: every device pointer in it points INTO the static array
+};
+constexpr int kMaxDev = 64;
+static Dev g_dev[kMaxDev];
+static std::mutex g_mu;
+
+// Once per device, with that device current: find the array's device address and fix the launch plan of the five kernels.
+// Nothing here allocates device memory (attribute and occupancy queries only).
+static int static_device(int device, Dev** out) {
+  Dev& d = g_dev[device];
+  *out = &d;
+  if (d.ready) return 0;
+  void* p = nullptr;
+  CUDA_TRY(cudaGetSymbolAddress(&p, g_pirl_static_ws));
+  if (!p || ((uintptr_t)p & 255)) return fail(-9, "static workspace: unexpected device address");
+  d.base = (unsigned char*)p;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  pirl_handle* h = &d.h;
+  h->ff = kFF; h->ld = kFF; h->maxrot = (int)kMaxRot; h->maxsw = (int)kMaxSw;
+  h->sm_count = prop.multiProcessorCount; h->smem_optin = prop.sharedMemPerBlockOptin;
+  const int optin = (int)(h->smem_optin - 1024);
+  const size_t budget = h->smem_optin - 1024, cmat = 2 * kM2 * sizeof(double);
+  // same attributes and sizes as pirl_rcwa_create picks for order 40 (so a handle on this device keeps its behaviour)
+  h->regtile = true; h->sub_size = 0;
+  CUDA_TRY(cudaFuncSetAttribute(rk_front<Cfg81>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+  CUDA_TRY(cudaFuncSetAttribute(k_ql, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+  CUDA_TRY(cudaFuncSetAttribute(RK_TAIL2, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+  CUDA_TRY(cudaFuncSetAttribute(k_tail<TAIL_NT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+  h->apply_rows = 96; h->apply_k = 4; h->apply_variant = 0;
+  h->apply_smem = (size_t)std::min(96, kFF) * apply_ld(kFF, 4) * 8;
+  CUDA_TRY(cudaFuncSetAttribute(k_apply<96, 4, 81>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(budget - 2 * (size_t)(256 + 2 * 4) * 4 * sizeof(cplx))));
+  CUDA_TRY(max_carveout(rk_front<Cfg81>)); CUDA_TRY(max_carveout(k_ql)); CUDA_TRY(max_carveout(k_apply<96, 4, 81>));
+  CUDA_TRY(max_carveout(RK_TAIL2)); CUDA_TRY(max_carveout(k_tail<TAIL_NT, 3>));
+  h->ql_smem = (size_t)2 * kFF * 32 * 8;
+  h->rk_tail2_smem = (size_t)Tail2Sm::doubles * 8;
+  int per_sm = 0;
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, RK_TAIL2, Cfg81T2::NT, h->rk_tail2_smem));
+  if (per_sm < 1) return fail(-9, "rk_tail2 does not fit on this device");
+  h->rk_tail2_grid = h->sm_count * per_sm;
+  h->rk_front_grid = h->sm_count;                 // rk_front_smem depends on n_cells: set per call
+  const size_t vec = (size_t)tail_vec_doubles(kFF) * 8;
+  h->tail_mats = mats_that_fit(budget, vec, cmat, 2);
+  h->tail_smem = vec + h->tail_mats * cmat;
+  h->tail_grid = kTailCtas;                        // the spill area below holds kTailCtas CTAs
+  // carve the array
+  h->d_tw = (cplx*)(d.base + oTw); h->d_Dk = (cplx*)(d.base + oDk);
+  h->Cbuf = (double*)(d.base + oC); h->Lbuf = (double*)(d.base + oL); h->Wbuf = (double*)(d.base + oW);
+  h->tri = (double*)(d.base + oTri); h->lam = (double*)(d.base + oLam);
+  h->rot_cs = (cplx*)(d.base + oRot); h->sweeps = (uint16_t*)(d.base + oSw);
+  h->scratch = (double*)(d.base + oSpill); h->scratch_stride = kSpillStride; h->scratch_ctas = kTailCtas;
+  int* cnt = (int*)(d.base + oCnt);
+  h->nrot = cnt; h->nsw = cnt + kMaxB; h->wstatus = cnt + 2 * kMaxB; h->queues = cnt + 3 * kMaxB;
+  d.ready = true;
+  return 0;
+}
+
+// twiddles exp(-2 pi i p / n_cells) and the zero-order-hold factor of the up-sampled pattern (the tables of pirl_rcwa_create)
+static void host_tables(int nc, std::vector<cplx>& tw, std::vector<cplx>& Dk) {
+  const long double PI = 3.141592653589793238462643383279502884L;
+  tw.resize(nc); Dk.resize(kFF);
+  for (int p = 0; p < nc; ++p) {
+    const long double a = -2.0L * PI * p / nc;
+    tw[p] = make_double2((double)cosl(a), (double)sinl(a));
+  }
+  const long double R = 4.0L * kOrder + 2.0L, M = R * nc;
+  for (int k = 0; k < kFF; ++k) {
+    std::complex<long double> v(k == 0 ? 1.0L : 0.0L, 0.0L);
+    if (k % nc != 0)
+      v = (1.0L - std::polar(1.0L, -2.0L * PI * k / nc)) / (R * (1.0L - std::polar(1.0L, -2.0L * PI * k / M)));
+    v /= (long double)nc;
+    Dk[k] = make_double2((double)v.real(), (double)v.imag());
+  }
+}
+}  // namespace pirl_static
+
+extern "C" int pirl_rcwa_eval_static(const pirl_cfg* cfg, const int8_t* patterns, const double* params, int32_t param_stride,
+                                     int64_t B, double* eff, double* de_r3, double* de_t3, int32_t* status, void* stream) {
+  using namespace pirl_static;
+  if (!cfg) return fail(-1, "null argument");
+  if (cfg->order != kOrder || cfg->pol != 1 || cfg->algo != 0 || cfg->theta_deg != 0.0 || cfg->precision != 0)
+    return fail(-13, "pirl_rcwa_eval_static covers TM, order 40, theta 0, algo 0, float64 only (use a pirl_rcwa_create handle otherwise)");
+  if (cfg->n_cells < 2 || cfg->n_cells > kMaxCells)
+    return fail(-13, "pirl_rcwa_eval_static: n_cells must be in [2, " + std::to_string(kMaxCells) + "] (PIRL_STATIC_MAX_CELLS)");
+  if (B < 0) return fail(-2, "negative batch");
+  if (B > kMaxB)
+    return fail(-13, "pirl_rcwa_eval_static: B = " + std::to_string(B) + " exceeds the static workspace of " + std::to_string(kMaxB) +
+                         " structures (PIRL_STATIC_MAX_BATCH): split the batch or use a pirl_rcwa_create handle");
+  if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
+  for (int r : cfg->reserved) if (r != 0) return fail(-12, "reserved fields of pirl_cfg must be zero");
+  if (B == 0) return 0;
+  if (!patterns || !params || !eff) return fail(-1, "null argument");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) return fail(e == cudaSuccess ? -7 : (int)e, "no CUDA device: this library has no CPU fallback");
+  if (cfg->device < 0 || cfg->device >= ndev || cfg->device >= kMaxDev) return fail(-8, "bad device ordinal");
+  CUDA_TRY(cudaSetDevice(cfg->device));
+  std::lock_guard<std::mutex> lock(g_mu);
+  Dev* d = nullptr;
+  if (int rc = static_device(cfg->device, &d)) return rc;
+  pirl_handle* h = &d->h;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nc = cfg->n_cells;
+  const size_t front_smem = (size_t)FrontSmem<Cfg81>::doubles(nc) * 8;
+  if (front_smem > h->smem_optin - 1024) return fail(-13, "pirl_rcwa_eval_static: n_cells too large for rk_front's shared memory");
+  h->cfg = *cfg; h->cfg.max_batch = kMaxB;
+  h->rk_front_smem = front_smem;
+  if (d->tab_cells != nc) {   // tables follow n_cells; uploaded in stream order, behind whatever an earlier call still runs
+    host_tables(nc, d->tw, d->Dk);
+    d->tab_cells = 0;
+    CUDA_TRY(cudaMemcpyAsync(h->d_tw, d->tw.data(), (size_t)nc * sizeof(cplx), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(h->d_Dk, d->Dk.data(), (size_t)kFF * sizeof(cplx), cudaMemcpyHostToDevice, st));
+    d->tab_cells = nc;
+  }
+  // the array keeps whatever the previous call left: rotation counts, sweep counts, status words and work counters start at zero
+  CUDA_TRY(cudaMemsetAsync(d->base + oCnt, 0, kCntBytes, st));
+  return launch_chunk(h, chunk_params(h, patterns, params, param_stride, (int)B, eff, de_r3, de_t3, status), (int)B, st);
 }
