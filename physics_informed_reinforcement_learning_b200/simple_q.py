@@ -106,6 +106,8 @@ class SimpleQTrainer:
         self.updates = 0
         self.last_target_sync = 0
         self.learn_credit_from = None   # timestep at which learning started (updates owed are counted from here)
+        self._updates_at_credit = 0     # learner updates already done when the credit started (non-zero after a resume)
+        self._resumed = False           # a full checkpoint was loaded: train() must not re-seed the RNGs it restored
         self.log_dir = log_dir
         self.obs = None
         self.max_efficiency = float("-inf")
@@ -201,8 +203,9 @@ class SimpleQTrainer:
         """Runs until ``total_timesteps`` GLOBAL env steps have been taken.  Returns a metrics dict."""
         env, cfg = self.env, self.cfg
         if self.obs is None:
-            np.random.seed(cfg.seed + self.rank)
-            torch.manual_seed(cfg.seed + self.rank)
+            if not self._resumed:         # fresh start only: a resumed run continues the RNG streams of its checkpoint
+                np.random.seed(cfg.seed + self.rank)
+                torch.manual_seed(cfg.seed + self.rank)
             self.obs = env.reset()
         per_iter = env.B * self.world
         losses = []
@@ -230,8 +233,10 @@ class SimpleQTrainer:
             if self.replay.size * self.world >= cfg.learning_starts:
                 if self.learn_credit_from is None:
                     self.learn_credit_from = self.timesteps - per_iter
+                    self._updates_at_credit = self.updates
                 # one learner update per `timesteps_per_update` sampled timesteps (configs/simple_q.py:71-73), never more
-                owed = (self.timesteps - self.learn_credit_from) // max(cfg.timesteps_per_update, 1) - self.updates
+                owed = ((self.timesteps - self.learn_credit_from) // max(cfg.timesteps_per_update, 1)
+                        - (self.updates - self._updates_at_credit))
                 if owed > cfg.max_updates_per_iter and not self.backlog_warned and self.rank == 0:
                     self.backlog_warned = True
                     print(f"[simple_q] {per_iter} timesteps per iteration owe {owed} learner updates, more than "
@@ -282,15 +287,21 @@ class SimpleQTrainer:
     # --------------------------------------------------------------------------------------------
     def save_checkpoint(self, path: str):
         """Policy, target, optimiser, counters and RNG state (the reference checkpoints through Ray AIR every iteration and
-        at the end, main.py:176-182).  Every rank holds the same policy; rank 0 writes."""
+        at the end, main.py:176-182).  Every rank holds the same policy; rank 0 writes.  COLLECTIVE when world > 1: every rank
+        must call it, because the exploration / replay generators differ per rank and are gathered into rank 0's file."""
+        rng = {"gen_state": self.gen.get_state().cpu(), "torch_rng": torch.get_rng_state(), "numpy_rng": np.random.get_state()}
+        rng_per_rank = [rng]
+        if self.world > 1:
+            rng_per_rank = [None] * self.world
+            dist.all_gather_object(rng_per_rank, rng)
         if self.rank != 0:
             return None
         os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
         state = {"model": self.model.state_dict(), "target": self.target.state_dict(), "optimizer": self.opt.state_dict(),
                  "timesteps": self.timesteps, "updates": self.updates, "last_target_sync": self.last_target_sync,
                  "learn_credit_from": self.learn_credit_from, "best_eff": self.best_eff, "best_pattern": self.best_pattern,
-                 "gen_state": self.gen.get_state(), "torch_rng": torch.get_rng_state(), "numpy_rng": np.random.get_state(),
-                 "config": dataclasses.asdict(self.cfg)}
+                 "gen_state": rng["gen_state"], "torch_rng": rng["torch_rng"], "numpy_rng": rng["numpy_rng"],
+                 "rng_per_rank": rng_per_rank, "config": dataclasses.asdict(self.cfg)}
         tmp = path + ".tmp"
         torch.save(state, tmp)
         os.replace(tmp, path)
@@ -306,11 +317,24 @@ class SimpleQTrainer:
             return state
         self.opt.load_state_dict(state["optimizer"])
         self.timesteps, self.updates = int(state["timesteps"]), int(state["updates"])
-        self.last_target_sync, self.learn_credit_from = state["last_target_sync"], state["learn_credit_from"]
+        self.last_target_sync = state["last_target_sync"]
+        # the replay buffer is not in the checkpoint: the update credit restarts when the refilled buffer reaches
+        # learning_starts again (otherwise the timesteps spent refilling would be paid back as one burst of updates on a
+        # nearly empty buffer, above the reference's one update per timesteps_per_update)
+        self.learn_credit_from = None
         self.best_eff, self.best_pattern = state["best_eff"], state["best_pattern"]
-        self.gen.set_state(state["gen_state"].cpu())
-        torch.set_rng_state(state["torch_rng"].cpu())
-        np.random.set_state(state["numpy_rng"])
+        per_rank = state.get("rng_per_rank") or [state]
+        if len(per_rank) == self.world:                   # same world size: every rank continues its own streams
+            mine = per_rank[self.rank]
+            self.gen.set_state(mine["gen_state"].cpu())
+            torch.set_rng_state(mine["torch_rng"].cpu())
+            np.random.set_state(mine["numpy_rng"])
+        else:                                             # world size changed: fresh, distinct, checkpoint-dependent streams
+            salt = self.cfg.seed + 1000 * self.rank + self.timesteps
+            self.gen.manual_seed(salt)
+            torch.manual_seed(salt + 1)
+            np.random.seed((salt + 2) % (2 ** 32))
+        self._resumed = True
         self._graph = None                # the captured learner graph holds the old parameter values' addresses: still valid,
         self._graph_warmup = 0            # but re-capture keeps the optimiser state and the graph consistent
         return state

@@ -169,3 +169,68 @@ def test_two_rank_gloo_keeps_weights_in_sync():
         assert ts >= 800 and upd > 10
         assert diff <= 1e-6                            # gradient all_reduce keeps every rank's policy identical
     assert res[0][4] == res[1][4]                      # max_efficiency reduced with MAX over ranks
+
+
+def _explore_draw(tr):
+    """Next exploration actions of a trainer at epsilon = 1: they depend on its private generator only, not on the policy."""
+    return tr.act(torch.ones(tr.env.B, tr.env.n_cells, dtype=torch.float64), 1.0).clone()
+
+
+def test_resume_continues_rng_streams_and_rebases_update_credit(tmp_path):
+    """A resumed run must continue the RNG streams stored in the checkpoint (train() used to re-seed them), and must not pay
+    back the timesteps spent refilling the empty replay buffer as one burst of learner updates."""
+    cfg = SimpleQConfig(learning_starts=64, train_batch_size=16, epsilon_timesteps=400, target_network_update_freq=64,
+                        replay_capacity=1024, timesteps_per_update=8, max_updates_per_iter=64)
+    tr = SimpleQTrainer(ToyEnv(8, n=16, horizon=8), FCNQNet(16, 32), cfg)
+    tr.train(8 * 20)
+    ck = tr.save_checkpoint(str(tmp_path / "ckpt.pt"))
+    np_next, torch_next = np.random.random(), torch.rand(1)          # what the uninterrupted run would draw next
+    want = _explore_draw(tr)
+    np.random.seed(999); torch.manual_seed(999)                       # the resuming process starts from unrelated RNG state
+    tr2 = SimpleQTrainer(ToyEnv(8, n=16, horizon=8), FCNQNet(16, 32), cfg)
+    tr2.load_checkpoint(ck)
+    tr2.train(tr2.timesteps)                                          # runs train()'s start-up code (reset), no iteration
+    assert np.random.random() == np_next and torch.equal(torch.rand(1), torch_next)
+    assert torch.equal(_explore_draw(tr2), want)
+    # update credit: while the buffer refills (64 transitions = 8 iterations) nothing is owed; afterwards one update per
+    # timesteps_per_update = one per iteration of 8 envs, never a catch-up burst
+    u0 = tr2.updates
+    tr2.train(tr2.timesteps + 8 * 8)
+    assert tr2.updates - u0 <= 1
+    tr2.train(tr2.timesteps + 8 * 5)
+    assert 4 <= tr2.updates - u0 <= 6
+
+
+def _resume_worker(rank, world, port, q, tmp):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = SimpleQConfig(learning_starts=32, train_batch_size=32, epsilon_timesteps=500, target_network_update_freq=64,
+                        replay_capacity=1024)
+    tr = SimpleQTrainer(ToyEnv(8, n=16, horizon=8, seed=0), FCNQNet(16, 32), cfg)
+    tr.train(160)
+    path = os.path.join(tmp, "ckpt.pt")
+    tr.save_checkpoint(path)                          # collective: every rank's generator goes into rank 0's file
+    dist.barrier()
+    want = _explore_draw(tr)
+    tr2 = SimpleQTrainer(ToyEnv(8, n=16, horizon=8, seed=0), FCNQNet(16, 32), cfg)
+    tr2.load_checkpoint(path)
+    tr2.train(tr2.timesteps)
+    got = _explore_draw(tr2)
+    q.put((rank, got.tolist(), want.tolist()))
+    dist.destroy_process_group()
+
+
+def test_two_rank_resume_keeps_per_rank_exploration_streams(tmp_path):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29850 + os.getpid() % 100
+    procs = [ctx.Process(target=_resume_worker, args=(r, 2, port, q, str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(30)
+    assert all(p.exitcode == 0 for p in procs)
+    for rank, got, want in res:
+        assert got == want                             # each rank continues ITS stream, as an uninterrupted run would
+    assert res[0][1] != res[1][1]                      # and the ranks do not share one stream after the resume

@@ -35,7 +35,9 @@ def main():
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--no_cuda_graph", action="store_true", help="run the learner step eagerly")
     ap.add_argument("--transfer_ckpt", type=str, default=None,
-                    help="checkpoint written by this script to resume from (main.py:163-164 algo.load_checkpoint)")
+                    help="checkpoint written by this script to resume from (main.py:163-164 algo.load_checkpoint): networks, optimiser, "
+                         "counters and every rank's RNG streams; the replay buffer is NOT stored, so learning pauses until "
+                         "the refilled buffer reaches learning_starts and the update credit restarts there")
     ap.add_argument("--transfer_weights_only", action="store_true",
                     help="with --transfer_ckpt: load the networks only (fresh optimiser, counters and exploration schedule)")
     ap.add_argument("--checkpoint_every", type=int, default=20000,
