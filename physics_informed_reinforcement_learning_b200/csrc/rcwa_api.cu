@@ -78,6 +78,9 @@ struct pirl_handle {
   int8_t* hd_patterns = nullptr; double* hd_params = nullptr; double* hd_out = nullptr; int32_t* hd_status = nullptr;
   int64_t hd_cap = 0;
   cudaStream_t own_stream = nullptr;
+  // the workspaces serve ONE evaluation at a time, but calls arrive on different streams (the caller's for the device entry
+  // points, own_stream for the *_host ones): evBusy marks the end of the last call, busy_stream the stream it ran on
+  cudaEvent_t evBusy = nullptr; cudaStream_t busy_stream = nullptr; bool busy_valid = false;
   // adjoint gradient (allocated on the first pirl_rcwa_eval_grad)
   double *g_lamb = nullptr, *g_Lf = nullptr, *g_Rf = nullptr, *g_Vf = nullptr, *g_Einv = nullptr, *g_scr_tail = nullptr, *g_scr_eig = nullptr;
   int g_eig_mma = 0;   // PIRL_GEIG_DMMA: GEMMs of g_eigback on mma.sync.m8n8k4.f64 tiles
@@ -115,6 +118,18 @@ using Cfg81T2 = TileCfg<81, 27, 9, 3, 9, 2>;  // real-arithmetic tail: one real 
 #define RK_TAIL2 rk_tail2<Cfg81T2, 56, 10, 5>
 using Tail2Sm = Tail2Smem<Cfg81T2, 56, 10, 5>;
 static constexpr int kTailMmax = 64;   // 64 keeps rk_tail + one k_ql CTA within one SM's shared memory
+
+// Takes the handle's workspaces over for one call on `st`: waits (on the device) for the previous call if that was issued on
+// another stream, and marks the end of this call when it goes out of scope.  Same-stream sequences pay one event record.
+struct StreamTurn {
+  pirl_handle* h; cudaStream_t st;
+  StreamTurn(pirl_handle* h_, cudaStream_t st_) : h(h_), st(st_) {
+    if (h->evBusy && h->busy_valid && h->busy_stream != st) cudaStreamWaitEvent(st, h->evBusy, 0);
+  }
+  ~StreamTurn() {
+    if (h->evBusy && cudaEventRecord(h->evBusy, st) == cudaSuccess) { h->busy_stream = st; h->busy_valid = true; }
+  }
+};
 
 static cudaEvent_t take_event(pirl_handle* h) {
   if (!h->ev_free.empty()) { cudaEvent_t e = h->ev_free.back(); h->ev_free.pop_back(); return e; }
@@ -167,6 +182,9 @@ static int smm_prepare(pirl_handle* h) {
   if (h->smm.ok) return 0;
   CUDA_TRY(smm_plan(h->ff, h->cfg.order, h->cfg.n_cells, h->sm_count, h->smem_optin - 1024, &h->smm));
   if (!h->smm.ok) return fail(-9, "k_smm does not fit on this device");
+  // one scratch block (44 ff^2 doubles: 14 MB at order 100) per persistent CTA; no launch ever has more than max_batch
+  // structures, so a small handle (the JLABCode drop-in caches max_batch = 64) must not pay for 2 x sm_count of them
+  h->smm.grid = std::min(h->smm.grid, h->cfg.max_batch);
   CUDA_TRY(dmalloc(&h->smm_scratch, (size_t)h->smm.grid * h->smm.scratch_doubles));
   return 0;
 }
@@ -386,6 +404,7 @@ extern "C" int pirl_rcwa_create(const pirl_cfg* cfg, pirl_handle** out) {
     for (int i = 0; i < pirl_handle::kSide; ++i) CUDA_TRY(cudaStreamCreateWithPriority(&h->side[i], cudaStreamNonBlocking, hi));
     for (int i = 0; i < pirl_handle::kSide; ++i) CUDA_TRY(cudaStreamCreateWithPriority(&h->fstream[i], cudaStreamNonBlocking, lo));
     CUDA_TRY(cudaEventCreateWithFlags(&h->evStart, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&h->evBusy, cudaEventDisableTiming));
     for (int i = 0; i < pirl_handle::kMaxSub; ++i) {
       CUDA_TRY(cudaEventCreateWithFlags(&h->evF[i], cudaEventDisableTiming));
       CUDA_TRY(cudaEventCreateWithFlags(&h->evQ[i], cudaEventDisableTiming));
@@ -414,6 +433,7 @@ extern "C" int pirl_rcwa_destroy(pirl_handle* h) {
   for (auto q : h->side) if (q) cudaStreamDestroy(q);
   for (auto q : h->fstream) if (q) cudaStreamDestroy(q);
   if (h->evStart) cudaEventDestroy(h->evStart);
+  if (h->evBusy) cudaEventDestroy(h->evBusy);
   for (auto e : h->evF) if (e) cudaEventDestroy(e);
   for (auto e : h->evQ) if (e) cudaEventDestroy(e);
   for (auto& p : h->ev_pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
@@ -686,6 +706,7 @@ extern "C" int pirl_rcwa_eval(pirl_handle* h, const int8_t* patterns, const doub
   if (param_stride != 0 && param_stride != 4) return fail(-3, "param_stride must be 0 or 4");
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
+  StreamTurn turn(h, st);
   const int64_t mb = h->cfg.max_batch;
   for (int64_t off = 0; off < B; off += mb) {
     const int Bc = (int)std::min<int64_t>(mb, B - off);
@@ -759,6 +780,7 @@ extern "C" int pirl_rcwa_eval_stack(pirl_handle* h, const int8_t* patterns, cons
   if (int rc = smm_prepare(h)) return rc;
   if (!h->stack_params) CUDA_TRY(dmalloc(&h->stack_params, (size_t)h->cfg.max_batch * 4));
   cudaStream_t st = (cudaStream_t)stream;
+  StreamTurn turn(h, st);
   const int L = n_layers, nc = h->cfg.n_cells;
   const int64_t per = h->cfg.max_batch / L;
   for (int64_t off = 0; off < B; off += per) {
@@ -963,6 +985,7 @@ extern "C" int pirl_rcwa_eval_grad(pirl_handle* h, const int8_t* patterns, const
   if (h->cfg.algo != 0 || h->cfg.pol != 1) return fail(-4, "the adjoint gradient is implemented for algo = 0 (ETM), TM only");
   if (int rc = grad_prepare(h)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  StreamTurn turn(h, st);
   const int64_t mb = h->cfg.max_batch;
   const int ff = h->ff;
   for (int64_t off = 0; off < B; off += mb) {

@@ -544,3 +544,27 @@ def test_layer_stacks_and_te_against_the_unmodified_reference(golden_dir, pkg):
         r = O.evaluate_stack(pats[i].astype(float), 1050.0, 55.0, 24, ths[i], 1, 'TMM')
         assert abs(eff[i] - r.eff) <= TIGHT and np.abs(t3[i] - r.de_ti[23:26]).max() <= TIGHT
     be.close()
+
+
+def test_device_and_host_entry_points_share_one_handle_safely(pkg, torch_mod):
+    """evaluate() is asynchronous on the caller's stream, evaluate_host() runs on the handle's own stream, and both use the
+    handle's workspaces: a host call issued while a device call is still running must wait for it (and the other way round)."""
+    torch = torch_mod
+    rng = np.random.default_rng(11)
+    be = pkg.RCWABatch(256, 40, max_batch=1024)
+    big = torch.from_numpy(rng.choice(np.array([-1, 1], dtype=np.int8), size=(1024, 256))).cuda()
+    small = rng.choice(np.array([-1, 1], dtype=np.int8), size=(3, 256))
+    want_big = be.evaluate(big).clone()
+    torch.cuda.synchronize()
+    want_small = be.evaluate_host(small).copy()
+    side = torch.cuda.Stream()
+    for _ in range(5):
+        got_big = be.evaluate(big)                       # ~2 ms of kernels in flight on the current stream ...
+        got_small = be.evaluate_host(small)              # ... while this call starts on the handle's own stream
+        with torch.cuda.stream(side):
+            got_side = be.evaluate(big[:64])             # and a third stream right behind it
+        torch.cuda.synchronize()
+        assert torch.equal(got_big, want_big)
+        assert np.array_equal(got_small, want_small)
+        assert torch.equal(got_side, want_big[:64])
+    be.close()
