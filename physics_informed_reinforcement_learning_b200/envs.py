@@ -122,6 +122,16 @@ def make(env_id='MeentIndex-v0', **kwargs):
     return MeentIndex(**kwargs)
 
 
+_STATUS_BITS = (1, 2, 4)      # PIRL_ST_EIG_NOT_CONVERGED, PIRL_ST_NONFINITE, PIRL_ST_NOT_POSDEF (include/pirl_rcwa.h)
+
+
+def status_flags(status, mask, acc):
+    """Bitwise OR of the per-structure status words, kept as one 0/1 flag per bit of ``mask`` and folded into ``acc``
+    (max of 0/1 flags = OR, which also all-reduces across ranks with MAX; the numeric max of the words is NOT their OR)."""
+    seen = ((status.reshape(-1, 1) & mask) != 0).any(dim=0).to(acc.dtype)
+    return acc.maximum(seen)
+
+
 class VectorDeflectorEnv:
     """B independent MeentIndex envs advanced by one batched RCWA launch per step (device resident)."""
 
@@ -155,7 +165,8 @@ class VectorDeflectorEnv:
         # solver status words (non-converged eigensolve, non-finite result, not positive definite): checked every N steps
         # (0 = never on the step path; check_status() on demand).  The reference raises LinAlgError instead.
         self.check_status_every = int(check_status_every)
-        self._status_acc = torch.zeros((), dtype=torch.int32, device=dev)
+        self._status_acc = torch.zeros(len(_STATUS_BITS), dtype=torch.int32, device=dev)   # one 0/1 flag per status bit
+        self._status_mask = torch.tensor(_STATUS_BITS, dtype=torch.int32, device=dev)
         self._steps = 0
         rows, _ = self.backend._params(1, float(wavelength), float(desired_angle), float(thickness), None)
         self.params = torch.from_numpy(rows).to(dev)
@@ -168,12 +179,18 @@ class VectorDeflectorEnv:
 
     def _evaluate(self, patterns):
         eff, st = self.backend.evaluate(patterns, params=self.params, return_status=True)
-        self._status_acc |= st.max() if st.numel() else 0       # device side, no sync
+        if st.numel():
+            self._status_acc = status_flags(st, self._status_mask, self._status_acc)       # device side, no sync
         return eff
 
     def check_status(self):
-        """Raise if any evaluation since the last check set a solver status bit (one device->host read)."""
-        bits = int(self._status_acc.item())
+        """Raise if any evaluation since the last check set a solver status bit (one device->host read).  With an initialised
+        process group of more than one rank this is a COLLECTIVE (the flags are all-reduced first), so that every rank raises
+        together instead of one rank leaving the others blocked in the next gradient all_reduce: call it on all ranks."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self._status_acc, op=dist.ReduceOp.MAX)
+        bits = int((self._status_acc * self._status_mask).sum().item())
         self._status_acc.zero_()
         if bits:
             raise FloatingPointError(f"RCWA solver status bits {bits:#x} set (1 = eigensolver not converged, 2 = non-finite "

@@ -129,3 +129,17 @@ def test_product_never_imports_the_oracle():
         if fn.endswith(".py"):
             src = open(os.path.join(pkg, fn)).read()
             assert "oracle" not in src.replace("oracle/make_golden.py", ""), fn
+
+
+def test_status_words_are_ored_bit_by_bit():
+    """A batch holding statuses 1 and 4 must report 5 (the numeric max, 4, would drop the eigensolver bit)."""
+    import torch
+    from physics_informed_reinforcement_learning_b200.envs import status_flags, _STATUS_BITS
+    mask = torch.tensor(_STATUS_BITS, dtype=torch.int32)
+    acc = torch.zeros(3, dtype=torch.int32)
+    acc = status_flags(torch.tensor([0, 1, 0, 4], dtype=torch.int32), mask, acc)
+    assert int((acc * mask).sum()) == 5
+    acc = status_flags(torch.tensor([0, 0], dtype=torch.int32), mask, acc)          # flags are sticky until cleared
+    assert int((acc * mask).sum()) == 5
+    acc = status_flags(torch.tensor([2 | 0x100], dtype=torch.int32), mask, acc)      # internal high bits are ignored
+    assert int((acc * mask).sum()) == 7
