@@ -370,6 +370,8 @@ def run_b200(args):
         barrier()
         for a, b in sev:
             flush.fill_(1)
+            if not args.no_sync_after_flush:      # same timing as the headline arm: the flush write-back stays outside the step
+                torch.cuda.synchronize()
             a.record()
             step(g_pats, g_out, G)
             b.record()
@@ -381,6 +383,48 @@ def run_b200(args):
     elif world == 1:
         strong = {"global_batch": args.batch, "structures_per_gpu": args.batch, "value": args.batch * args.steps / job_s,
                   "unit": UNIT, "ms_per_step": job_s / args.steps * 1e3, "note": "N = 1: same run as `value`"}
+
+    # ---- the other BASELINE configurations, briefly (not part of `value`): configs[4] (order 100, 512 cells: the cluster
+    #      kernels), the configs[3] size (order 60, forward + adjoint gradient) and the S-matrix operator at the headline size.
+    #      Each is a RATE on a bounded number of structures per GPU (stated), device resident, L2 flushed between steps, timed
+    #      with CUDA events, max over ranks; only in the default (headline) run so that the driver's record carries them --------
+    other = None
+    if (args.n_cells, args.order, args.algo) == (256, 40, "TMM") and not args.no_other_configs:
+        other = {}
+        legs = [("configs[4] order 100 / 512 cells", dict(n_cells=512, order=100, algo="TMM"), 2048, 512, False),
+                ("configs[3] size: order 60 / 256 cells", dict(n_cells=256, order=60, algo="TMM"), 4096, 4096, True),
+                ("algo SMM (Redheffer star products), order 40 / 256 cells", dict(n_cells=256, order=40, algo="SMM"), 4096, 4096, False)]
+        for tag, kw, nb, chunk, with_grad in legs:
+            ob = RCWABatch(max_batch=chunk, device=local_rank, **kw)
+            op = torch.from_numpy(make_patterns(nb, kw["n_cells"], 4321 + rank)).to(dev)
+            osteps = 2
+
+            def timed(fn):
+                fn(); torch.cuda.synchronize()                     # warm-up (first call also sizes lazily allocated buffers)
+                tot = 0.0
+                for _ in range(osteps):
+                    flush.fill_(1); torch.cuda.synchronize()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(); out = fn(); b.record(); torch.cuda.synchronize()
+                    tot += a.elapsed_time(b) * 1e-3
+                return max_over_ranks(tot, device=dev), out
+
+            l_0 = ob.launch_count()
+            t_s, (oe, ost) = timed(lambda: ob.evaluate(op, params=d_params, return_status=True))
+            assert int(ost.abs().sum()) == 0 and bool(torch.isfinite(oe).all()), tag
+            ff_o = 2 * kw["order"] + 1
+            rec = {"structures_per_gpu_per_step": nb, "chunk": chunk, "steps": osteps, "value": nb * world * osteps / t_s,
+                   "unit": UNIT, "ms_per_step": t_s / osteps * 1e3, "gpu_launches": int(ob.launch_count() - l_0),
+                   "fp64_frac_by_f_alg": nb * osteps / t_s * f_alg(ff_o) / 1e12 / fp64_peak if fp64_peak else None}
+            if with_grad:
+                t_g, (ge, gg, gst) = timed(lambda: ob.evaluate_grad(op, params=d_params))
+                assert float((ge - oe).abs().max()) <= 1e-9 and int(gst.abs().sum()) == 0, tag
+                rec["adjoint_grad"] = {"value": nb * world * osteps / t_g, "unit": "gradients/s (efficiency + d eff / d 256 cells)",
+                                       "ms_per_step": t_g / osteps * 1e3}
+            other[tag] = rec
+            ob.close()
+            del ob, op
+            torch.cuda.empty_cache()
 
     # ---- single-call latency (BASELINE configs[0]): one MeentIndex.get_efficiency call, host buffers in and out ----------
     latency = None
@@ -459,7 +503,8 @@ def run_b200(args):
                        "thickness_nm": args.thickness, "chunk": max_batch, "algo": args.algo,
                        "parallelism": f"structures sharded over {world} GPU(s)"
                                       + ("; one NCCL all_gather of the float64 efficiencies per step, inside the timed region" if world > 1 else ""),
-                       "l2": "384 MiB flush between timed iterations; workspaces exceed L2"},
+                       "l2": "384 MiB flush between timed iterations; workspaces exceed L2",
+                       "sync_after_flush": not args.no_sync_after_flush},   # applies to `value` and to the `strong` leg alike
             "e2e": {"value": total_evals / e2e_job_s, "unit": UNIT,
                     "h2d_bytes_per_step": int(hp.nbytes + 32), "d2h_bytes_per_step": int(he.nbytes + hs.nbytes),
                     "ms_per_step": e2e_job_s / args.steps * 1e3},
@@ -473,6 +518,8 @@ def run_b200(args):
         line["strong"] = strong
     if latency is not None:
         line["latency"] = latency
+    if other is not None:
+        line["other_configs"] = other
     emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -519,6 +566,7 @@ def main():
     ap.add_argument("--max-batch", type=int, default=0, help="structures per internal chunk (0: batch, or 4096 beyond order 60)")
     ap.add_argument("--strong-batch", type=int, default=0, help="fixed GLOBAL batch of the strong-scaling leg (0: --batch)")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the short legs on BASELINE configs[4] / configs[3] size / algo SMM")
     ap.add_argument("--no-latency", action="store_true", help="skip the single-call latency leg (N = 1)")
     ap.add_argument("--no-sync-after-flush", action="store_true", help="experiment: no device sync between the (untimed) L2 flush and the timed step")
     args = ap.parse_args()
