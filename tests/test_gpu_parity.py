@@ -568,3 +568,40 @@ def test_device_and_host_entry_points_share_one_handle_safely(pkg, torch_mod):
         assert np.array_equal(got_small, want_small)
         assert torch.equal(got_side, want_big[:64])
     be.close()
+
+
+def test_env_kernels_reproduce_reference_step_fixtures(golden_dir, torch_mod):
+    """pirl_env_flip / pirl_env_reward through the C ABI against trajectories produced by the reference's own flip / step
+    method objects (oracle/make_env_step_golden.py): every (state, action) -> state bit-exact, out-of-range actions
+    included; reward = eff_new - eff_prev bit-exact in float64 from the recorded efficiencies."""
+    import ctypes as C
+    from physics_informed_reinforcement_learning_b200 import _lib as lib_mod
+    torch = torch_mod
+    lib = lib_mod.load()
+    g = np.load(os.path.join(golden_dir, "env_step_golden.npz"))
+    K, T = g["actions"].shape
+    pats = torch.from_numpy(g["init"].astype(np.int8)).cuda()                 # the K trajectories advance as one batch
+    prev = torch.from_numpy(g["effs"][:, 0].copy()).cuda()
+    rew = torch.empty(K, dtype=torch.float64, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for t in range(T):
+        acts = torch.from_numpy(g["actions"][:, t].astype(np.int64)).cuda()
+        lib_mod.check(lib.pirl_env_flip(pats.data_ptr(), acts.data_ptr(), K, 256, st))
+        new = torch.from_numpy(g["effs"][:, t + 1].copy()).cuda()
+        lib_mod.check(lib.pirl_env_reward(new.data_ptr(), prev.data_ptr(), rew.data_ptr(), None, None, pats.data_ptr(), K, 256, st))
+        torch.cuda.synchronize()
+        assert np.array_equal(pats.cpu().numpy(), g["states"][:, t].astype(np.int8)), t
+        assert np.array_equal(rew.cpu().numpy(), g["rewards"][:, t]), t
+        assert np.array_equal(prev.cpu().numpy(), g["effs"][:, t + 1]), t      # eff_prev <- eff_new
+
+
+def test_smm_operator_against_sixteen_reference_smm_runs(golden_dir, pkg):
+    """k_smm (algo='SMM') against 16 outputs of the unmodified reference run with algo='SMM' at order 60
+    (tests/golden/rcwa_smm_golden.npz, oracle/make_smm_golden.py), per-structure wavelength / angle / thickness rows."""
+    g = np.load(os.path.join(golden_dir, "rcwa_smm_golden.npz"))
+    be = pkg.RCWABatch(256, int(g["order"]), max_batch=16, algo='SMM')
+    eff, r3, t3, st = be.evaluate_host(g["patterns"], g["wavelength"], g["angle"], g["thickness"], return_orders=True)
+    assert not st.any()
+    assert np.abs(eff - g["ref_eff"]).max() <= TOL and np.abs(eff - g["ref_eff"]).max() <= TIGHT
+    assert np.abs(t3[:, ::-1] - g["ref_tran_cut"]).max() <= TIGHT and np.abs(r3[:, ::-1] - g["ref_refl_cut"]).max() <= TIGHT
+    be.close()

@@ -143,3 +143,18 @@ def test_status_words_are_ored_bit_by_bit():
     assert int((acc * mask).sum()) == 5
     acc = status_flags(torch.tensor([2 | 0x100], dtype=torch.int32), mask, acc)      # internal high bits are ignored
     assert int((acc * mask).sum()) == 7
+
+
+def test_env_oracle_reproduces_reference_step_fixtures(golden_dir):
+    """oracle/env_oracle.py against trajectories produced by the reference's own flip / reset / step method objects
+    (oracle/make_env_step_golden.py): states, efficiencies and rewards bit for bit, out-of-range actions included."""
+    from oracle.make_env_step_golden import stub_efficiency
+    g = np.load(os.path.join(golden_dir, "env_step_golden.npz"))
+    for k, seed in enumerate(g["seeds"]):
+        np.random.seed(int(seed))
+        env = env_oracle.ScalarEnv(stub_efficiency)
+        assert np.array_equal(env.reset(), g["init"][k]) and env.eff == g["effs"][k][0]
+        for t, a in enumerate(g["actions"][k]):
+            s, r, d, _ = env.step(int(a))
+            assert np.array_equal(s, g["states"][k][t])
+            assert r == g["rewards"][k][t] and env.eff == g["effs"][k][t + 1] and d == bool(g["dones"][k][t])

@@ -109,3 +109,18 @@ def test_stack_restatement_matches_reference_fixtures(golden_dir):
     a = O.evaluate_stack(s, 1100.0, 60.0, 20, th, 1, 'SMM').eff
     b = O.evaluate_stack(s[::-1], 1100.0, 60.0, 20, th[::-1], 1, 'TMM').eff
     assert abs(a - b) <= 1e-11 and abs(a - float(g["ML2_block16_N20_SMM/ref_eff"])) <= 1e-12
+
+
+def test_oracle_smm_against_sixteen_reference_smm_runs(golden_dir):
+    """The oracle's S-matrix form (solve_stack, algo='SMM') against 16 outputs of the unmodified reference run with
+    algo='SMM' at order 60 (oracle/make_smm_golden.py): blocky and random patterns, mixed wavelength / angle / thickness."""
+    import os
+    import numpy as np
+    from oracle import rcwa_oracle as O
+    g = np.load(os.path.join(golden_dir, "rcwa_smm_golden.npz"))
+    order = int(g["order"])
+    for i in range(len(g["ref_eff"])):
+        r = O.evaluate_stack(g["patterns"][i][None, :], float(g["wavelength"][i]), float(g["angle"][i]), order,
+                             (float(g["thickness"][i]),), 1, 'SMM')
+        assert abs(r.eff - g["ref_eff"][i]) <= 1e-12
+        assert np.abs(r.tran_cut - g["ref_tran_cut"][i]).max() <= 1e-12 and np.abs(r.refl_cut - g["ref_refl_cut"][i]).max() <= 1e-12
