@@ -182,7 +182,7 @@ static int smm_prepare(pirl_handle* h) {
   if (h->smm.ok) return 0;
   CUDA_TRY(smm_plan(h->ff, h->cfg.order, h->cfg.n_cells, h->sm_count, h->smem_optin - 1024, &h->smm));
   if (!h->smm.ok) return fail(-9, "k_smm does not fit on this device");
-  // one scratch block (44 ff^2 doubles: 14 MB at order 100) per persistent CTA; no launch ever has more than max_batch
+  // one scratch block (36 ff^2 doubles: 11.6 MB at order 100) per persistent CTA; no launch ever has more than max_batch
   // structures, so a small handle (the JLABCode drop-in caches max_batch = 64) must not pay for 2 x sm_count of them
   h->smm.grid = std::min(h->smm.grid, h->cfg.max_batch);
   CUDA_TRY(dmalloc(&h->smm_scratch, (size_t)h->smm.grid * h->smm.scratch_doubles));

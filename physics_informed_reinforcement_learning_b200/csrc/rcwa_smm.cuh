@@ -17,12 +17,14 @@
 #include "rcwa_common.cuh"
 
 constexpr int SMM_NT = 256;
-constexpr int SMM_NMAT = 21;          // complex ff x ff blocks of per-CTA scratch
+constexpr int SMM_NMAT = 17;          // complex ff x ff blocks of per-CTA scratch
 
 __host__ __device__ inline size_t smm_scratch_doubles(int ff) { return (size_t)SMM_NMAT * 2 * ff * ff + 2 * (size_t)ff * ff; }
-// shared: cre, cim [2N+1], per-harmonic complex diagonals vg, vr, vt, kzr, kzt, q, X [ff each], pattern bits, pivot slot
+// shared: cre, cim [2N+1], per-harmonic complex diagonals vg, vr, vt, kzr, kzt, q, X, the four diagonal S-blocks of a half
+// space (d11, d12, d21, d22) and the pivot column of the inverse [ff each], pattern bits, pivot slot
+constexpr int SMM_NVEC = 12;
 __host__ __device__ inline int smm_smem_doubles(int ff, int N, int n_cells) {
-  return pirl_even(2 * (2 * N + 1)) + 2 * 7 * ff + pirl_even((n_cells + 7) / 8) + 8;
+  return pirl_even(2 * (2 * N + 1)) + 2 * SMM_NVEC * ff + pirl_even((n_cells + 7) / 8) + 8;
 }
 
 // C = A B  (n x n complex, row major); each thread owns 2 x 2 output blocks
@@ -71,90 +73,192 @@ __device__ __forceinline__ void smm_scale(cplx* C, const cplx* dl, const cplx* A
   __syncthreads();
 }
 
+// pivot of column k among rows >= k (largest |re| + |im|, lowest row on ties) -> *slot (-1: the column is zero); warp 0 only
+__device__ __forceinline__ void smm_pivot_search(const cplx* __restrict__ A, int n, int k, int lane, int* slot) {
+  double best = -1.0; int bi = k;
+  for (int i = k + lane; i < n; i += 32) {
+    const cplx v = A[(size_t)i * n + k];
+    const double mg = fabs(v.x) + fabs(v.y);
+    if (mg > best) { best = mg; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  if (lane == 0) *slot = (best > 0.0) ? bi : -1;
+}
+
 // Ainv = A^-1 by Gauss-Jordan with partial pivoting on [A | I]; A is destroyed.  Returns (to every thread) whether a zero
-// pivot was met.  `slot`: one shared int.
-__device__ __forceinline__ bool smm_inverse(cplx* __restrict__ Ainv, cplx* __restrict__ A, int n, int tid, int* slot) {
-  const int lane = tid & 31, warp = tid >> 5;
-  constexpr int NW = SMM_NT / 32;
+// pivot was met.  `slot`: one shared int, `fcol`: n shared complex numbers.
+// One thread owns one COLUMN of [A | I] through a step (row swap, pivot-row scaling and elimination touch that column only), so
+// a step needs two barriers: the multipliers (column k) are staged in `fcol` first, and the owner of column k + 1 finds the
+// next pivot while it eliminates.  Rows are processed eight at a time, loads before stores, to keep eight L2 requests in flight.
+__device__ __forceinline__ bool smm_inverse(cplx* __restrict__ Ainv, cplx* __restrict__ A, int n, int tid, int* slot,
+                                            cplx* __restrict__ fcol) {
   bool singular = false;
   for (int idx = tid; idx < n * n; idx += SMM_NT) Ainv[idx] = make_double2((idx / n == idx % n) ? 1.0 : 0.0, 0.0);
+  if (tid < 32) smm_pivot_search(A, n, 0, tid, slot);
   __syncthreads();
   for (int k = 0; k < n; ++k) {
-    if (warp == 0) {
-      double best = -1.0; int bi = k;
-      for (int i = k + lane; i < n; i += 32) {
-        const cplx v = A[(size_t)i * n + k];
-        const double mg = fabs(v.x) + fabs(v.y);
-        if (mg > best) { best = mg; bi = i; }
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-      }
-      if (lane == 0) *slot = (best > 0.0) ? bi : -1;
-    }
-    __syncthreads();
     const int pv = *slot;
-    if (pv < 0) { singular = true; __syncthreads(); continue; }
-    if (pv != k) {
-      for (int j = tid; j < 2 * n; j += SMM_NT) {
-        cplx* M = (j < n) ? A : Ainv;
-        const int jj = (j < n) ? j : j - n;
-        const cplx t0 = M[(size_t)k * n + jj]; M[(size_t)k * n + jj] = M[(size_t)pv * n + jj]; M[(size_t)pv * n + jj] = t0;
-      }
+    if (pv >= 0) for (int i = tid; i < n; i += SMM_NT) fcol[i] = A[(size_t)i * n + k];
+    __syncthreads();
+    if (pv < 0) {                                       // zero column: flag it and look at the next one
+      singular = true;
+      if (tid < 32 && k + 1 < n) smm_pivot_search(A, n, k + 1, tid, slot);
+      __syncthreads();
+      continue;
     }
-    __syncthreads();
-    const cplx pinv = cinv(A[(size_t)k * n + k]);
-    __syncthreads();
-    for (int j = tid; j < 2 * n; j += SMM_NT) {        // scale the pivot row
-      cplx* M = (j < n) ? A : Ainv;
-      const int jj = (j < n) ? j : j - n;
-      M[(size_t)k * n + jj] = cmul(M[(size_t)k * n + jj], pinv);
-    }
-    __syncthreads();
-    for (int i = warp; i < n; i += NW) {               // eliminate column k from every other row
-      if (i == k) continue;
-      const cplx f = A[(size_t)i * n + k];
-      __syncwarp();
-      for (int j = lane; j < 2 * n; j += 32) {
-        cplx* M = (j < n) ? A : Ainv;
-        const int jj = (j < n) ? j : j - n;
-        if (j < n && jj <= k) { if (jj == k) M[(size_t)i * n + jj] = make_double2(0.0, 0.0); continue; }   // finished columns
-        M[(size_t)i * n + jj] = cfnma(f, M[(size_t)k * n + jj], M[(size_t)i * n + jj]);
+    const cplx pinv = cinv(fcol[pv]);
+    const cplx fswap = fcol[k];                         // multiplier of the row that moves from k to pv
+    for (int c = tid; c < 2 * n; c += SMM_NT) {
+      const bool inA = c < n;
+      if (inA && c <= k) continue;                      // finished columns of A are never read again
+      cplx* col = inA ? A + c : Ainv + (c - n);
+      const cplx a = col[(size_t)k * n];
+      cplx pk;
+      if (pv != k) { pk = cmul(col[(size_t)pv * n], pinv); col[(size_t)pv * n] = a; }
+      else pk = cmul(a, pinv);
+      col[(size_t)k * n] = pk;
+      const bool track = inA && c == k + 1;             // this thread finds the pivot of the next step
+      double best = -1.0; int bi = k + 1;
+      for (int i0 = 0; i0 < n; i0 += 8) {
+        cplx v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { const int i = i0 + u; if (i < n && i != k) v[u] = col[(size_t)i * n]; }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = i0 + u;
+          if (i < n && i != k) {
+            const cplx r = cfnma((i == pv) ? fswap : fcol[i], pk, v[u]);
+            col[(size_t)i * n] = r;
+            if (track && i > k) { const double mg = fabs(r.x) + fabs(r.y); if (mg > best) { best = mg; bi = i; } }
+          }
+        }
       }
+      if (track) *slot = (best > 0.0) ? bi : -1;
     }
     __syncthreads();
   }
   return singular;
 }
 
+// C = dl (.) A (.) dr (+ add) (+ diag(dg)): row scaling by dl, column scaling by dr (either may be null), optional addend and
+// diagonal
+__device__ __forceinline__ void smm_scale_add(cplx* C, const cplx* dl, const cplx* A, const cplx* dr, const cplx* add, const cplx* dg,
+                                              int n, int tid) {
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {
+    const int i = idx / n, j = idx - i * n;
+    cplx v = A[idx];
+    if (dl) v = cmul(dl[i], v);
+    if (dr) v = cmul(v, dr[j]);
+    if (add) v = cadd(v, add[idx]);
+    if (dg && i == j) v = cadd(v, dg[i]);
+    C[idx] = v;
+  }
+  __syncthreads();
+}
+
 // RedhefferStar (smm_util.py:289-318): OUT = SA (*) SB.  Blocks are {S11, S12, S21, S22}; T0..T3 are temporaries.
-// Returns whether an inverse met a zero pivot.
+// Returns whether an inverse met a zero pivot.  The reference inverts both I - SB11 SA22 (D) and I - SA22 SB11 (F); here
+// F = I + SA22 D SB11 (push-through identity), one inverse per star product.
 __device__ __forceinline__ bool smm_redheffer(cplx* const (&O)[4], cplx* const (&SA)[4], cplx* const (&SB)[4], cplx* T0, cplx* T1,
-                                              cplx* T2, cplx* T3, int n, int tid, int* slot) {
+                                              cplx* T2, cplx* T3, int n, int tid, int* slot, cplx* fcol) {
   bool sing = false;
-  // D_i = inv(I - SB11 SA22)
   smm_gemm(T0, SB[0], SA[3], n, tid);
   smm_axpby(T0, -1.0, T0, 0.0, nullptr, 1.0, n, tid);
-  sing |= smm_inverse(T1, T0, n, tid, slot);                   // T1 = D_i
-  // F_i = inv(I - SA22 SB11)
-  smm_gemm(T0, SA[3], SB[0], n, tid);
-  smm_axpby(T0, -1.0, T0, 0.0, nullptr, 1.0, n, tid);
-  sing |= smm_inverse(T2, T0, n, tid, slot);                   // T2 = F_i
-  // S11 = SA11 + SA12 D_i SB11 SA21 ; S12 = SA12 D_i SB12
-  smm_gemm(T0, SA[1], T1, n, tid);                             // T0 = SA12 D_i
-  smm_gemm(O[1], T0, SB[1], n, tid);
-  smm_gemm(T3, T0, SB[0], n, tid);
-  smm_gemm(T0, T3, SA[2], n, tid);
-  smm_axpby(O[0], 1.0, SA[0], 1.0, T0, 0.0, n, tid);
-  // S21 = SB21 F_i SA21 ; S22 = SB22 + SB21 F_i SA22 SB12
-  smm_gemm(T0, SB[2], T2, n, tid);                             // T0 = SB21 F_i
-  smm_gemm(O[2], T0, SA[2], n, tid);
-  smm_gemm(T3, T0, SA[3], n, tid);
+  sing |= smm_inverse(T1, T0, n, tid, slot, fcol);             // T1 = D = inv(I - SB11 SA22)
+  smm_gemm(T2, T1, SB[0], n, tid);                             // T2 = D SB11
+  smm_gemm(T3, T1, SB[1], n, tid);                             // T3 = D SB12
+  // S12 = SA12 D SB12 ; S11 = SA11 + SA12 D SB11 SA21
+  smm_gemm(O[1], SA[1], T3, n, tid);
+  smm_gemm(T0, SA[1], T2, n, tid);
+  smm_gemm(T1, T0, SA[2], n, tid);
+  smm_axpby(O[0], 1.0, SA[0], 1.0, T1, 0.0, n, tid);
+  // F = I + SA22 D SB11 ; S21 = SB21 F SA21 ; S22 = SB22 + SB21 F SA22 SB12
+  smm_gemm(T0, SA[3], T2, n, tid);
+  smm_axpby(T0, 1.0, T0, 0.0, nullptr, 1.0, n, tid);           // T0 = F
+  smm_gemm(T1, SB[2], T0, n, tid);                             // T1 = SB21 F
+  smm_gemm(O[2], T1, SA[2], n, tid);
+  smm_gemm(T3, T1, SA[3], n, tid);
   smm_gemm(T0, T3, SB[1], n, tid);
   smm_axpby(O[3], 1.0, SB[3], 1.0, T0, 0.0, n, tid);
+  return sing;
+}
+
+// OUT = SA (*) SB where every block of SA is DIAGONAL (a half space, S_RT of smm_util.py:70-85): a11, a12, a21, a22 are its
+// diagonals.  Products with a diagonal block are scalings: four GEMMs and one inverse.
+__device__ __forceinline__ bool smm_redheffer_diag_left(cplx* const (&O)[4], const cplx* a11, const cplx* a12, const cplx* a21,
+                                                        const cplx* a22, cplx* const (&SB)[4], cplx* T0, cplx* T1, cplx* T2, cplx* T3,
+                                                        int n, int tid, int* slot, cplx* fcol) {
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {           // T0 = I - SB11 a22
+    const int i = idx / n, j = idx - i * n;
+    const cplx v = cmul(SB[0][idx], a22[j]);
+    T0[idx] = make_double2(((i == j) ? 1.0 : 0.0) - v.x, -v.y);
+  }
+  __syncthreads();
+  const bool sing = smm_inverse(T1, T0, n, tid, slot, fcol);  // T1 = D
+  smm_gemm(T2, T1, SB[0], n, tid);                             // T2 = D SB11
+  smm_gemm(T3, T1, SB[1], n, tid);                             // T3 = D SB12
+  smm_scale_add(O[0], a12, T2, a21, nullptr, a11, n, tid);     // S11 = a11 + a12 D SB11 a21
+  smm_scale_add(O[1], a12, T3, nullptr, nullptr, nullptr, n, tid);   // S12 = a12 D SB12
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {           // T0 = F = I + a22 D SB11
+    const int i = idx / n, j = idx - i * n;
+    const cplx v = cmul(a22[i], T2[idx]);
+    T0[idx] = make_double2(((i == j) ? 1.0 : 0.0) + v.x, v.y);
+  }
+  __syncthreads();
+  smm_gemm(T1, SB[2], T0, n, tid);                             // T1 = SB21 F
+  smm_scale_add(O[2], nullptr, T1, a21, nullptr, nullptr, n, tid);   // S21 = SB21 F a21
+  smm_scale_add(T0, nullptr, T1, a22, nullptr, nullptr, n, tid);     // T0 = SB21 F a22
+  smm_gemm(T2, T0, SB[1], n, tid);
+  smm_axpby(O[3], 1.0, SB[3], 1.0, T2, 0.0, n, tid);           // S22 = SB22 + SB21 F a22 SB12
+  return sing;
+}
+
+// Column `z` of S11 and S21 of SA (*) SB where every block of SB is DIAGONAL (b11, b12, b21, b22): all the last star product
+// has to deliver (the incident field is the single harmonic z).  With D = inv(I - b11 SA22), u = b11 (.) SA21[:, z], v = D u:
+//   S11[:, z] = SA11[:, z] + SA12 v            S21[:, z] = b21 (.) (SA21[:, z] + SA22 v)        (F x = x + SA22 D b11 x)
+// One inverse and matrix-vector products.  `u`, `v`: n shared complex numbers each, `pa`, `pb`: three each (n may be as small
+// as 3); results for `rows[0..3)` only.
+__device__ __forceinline__ bool smm_redheffer_diag_right_col(cplx (&s11)[3], cplx (&s21)[3], const int (&rows)[3], cplx* const (&SA)[4],
+                                                             const cplx* b11, const cplx* b21, int z, cplx* T0, cplx* T1, cplx* u,
+                                                             cplx* v, cplx* pa, cplx* pb, int n, int tid, int* slot, cplx* fcol) {
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {           // T0 = I - b11 SA22
+    const int i = idx / n, j = idx - i * n;
+    const cplx w = cmul(b11[i], SA[3][idx]);
+    T0[idx] = make_double2(((i == j) ? 1.0 : 0.0) - w.x, -w.y);
+  }
+  for (int i = tid; i < n; i += SMM_NT) u[i] = cmul(b11[i], SA[2][(size_t)i * n + z]);
+  __syncthreads();
+  const bool sing = smm_inverse(T1, T0, n, tid, slot, fcol);  // T1 = D
+  const int lane = tid & 31, warp = tid >> 5;
+  for (int i = warp; i < n; i += SMM_NT / 32) {                // v = D u, one warp per row
+    cplx acc = make_double2(0, 0);
+    for (int j = lane; j < n; j += 32) acc = cfma(T1[(size_t)i * n + j], u[j], acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { acc.x += __shfl_xor_sync(0xffffffffu, acc.x, o); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, o); }
+    if (lane == 0) v[i] = acc;
+  }
+  __syncthreads();
+  if (warp < 6) {                                              // six dot products: rows[r] of SA12 v and of SA22 v
+    const int r = warp % 3, i = rows[r];
+    const cplx* Mrow = ((warp < 3) ? SA[1] : SA[3]) + (size_t)i * n;
+    cplx acc = make_double2(0, 0);
+    for (int j = lane; j < n; j += 32) acc = cfma(Mrow[j], v[j], acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { acc.x += __shfl_xor_sync(0xffffffffu, acc.x, o); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, o); }
+    if (lane == 0) ((warp < 3) ? pa : pb)[r] = acc;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int i = rows[r];
+    s11[r] = cadd(SA[0][(size_t)i * n + z], pa[r]);
+    s21[r] = cmul(b21[i], cadd(SA[2][(size_t)i * n + z], pb[r]));
+  }
   return sing;
 }
 
@@ -187,7 +291,12 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
   cplx* kzt = kzr + ff;
   cplx* qv = kzt + ff;
   cplx* Xv = qv + ff;
-  uint8_t* su = reinterpret_cast<uint8_t*>(Xv + ff);
+  cplx* d11 = Xv + ff;                 // diagonal S-blocks of the half space being attached (reflection, then transmission)
+  cplx* d12 = d11 + ff;
+  cplx* d21 = d12 + ff;
+  cplx* d22 = d21 + ff;
+  cplx* fcol = d22 + ff;               // pivot column of smm_inverse
+  uint8_t* su = reinterpret_cast<uint8_t*>(fcol + ff);
   int* slot = reinterpret_cast<int*>(su + 8 * pirl_even((nc + 7) / 8));
   cplx* base = reinterpret_cast<cplx*>(smm_scratch + (size_t)blockIdx.x * smm_scratch_doubles(ff));
   const size_t m2 = (size_t)n * n;
@@ -212,22 +321,16 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
     }
     __syncthreads();
     cplx *A = M[0], *B = M[1], *Ai = M[2], *T0 = M[3], *T1 = M[4], *T2 = M[5], *T3 = M[6], *SL11 = M[7], *SL12 = M[8];
-    cplx* R[4] = {M[9], M[10], M[11], M[12]};
-    cplx* G[4] = {M[13], M[14], M[15], M[16]};
-    cplx* H[4] = {M[17], M[18], M[19], M[20]};
-    // S_RT of the reflection region (A_B_matrices_half_space + S_RT, ref_mode = True): diagonal blocks, kept as matrices
-    for (int idx = tid; idx < n * n; idx += SMM_NT) {
-      const int i = idx / n, j = idx - i * n;
-      cplx s11 = make_double2(0, 0), s12 = s11, s21 = s11, s22 = s11;
-      if (i == j) {
-        const cplx rr = cmul(cinv(vg[i]), vr[i]);
-        const cplx a = make_double2(1.0 + rr.x, rr.y), bb = make_double2(1.0 - rr.x, -rr.y), ai = cinv(a);
-        s11 = cmul(make_double2(-bb.x, -bb.y), ai);
-        s12 = cscale(ai, 2.0);
-        s21 = cscale(csub(a, cmul(cmul(bb, ai), bb)), 0.5);
-        s22 = cmul(bb, ai);
-      }
-      R[0][idx] = s11; R[1][idx] = s12; R[2][idx] = s21; R[3][idx] = s22;
+    cplx* G[4] = {M[9], M[10], M[11], M[12]};
+    cplx* H[4] = {M[13], M[14], M[15], M[16]};
+    // S_RT of the reflection region (A_B_matrices_half_space + S_RT, ref_mode = True): four diagonal blocks
+    for (int i = tid; i < n; i += SMM_NT) {
+      const cplx rr = cmul(cinv(vg[i]), vr[i]);
+      const cplx a = make_double2(1.0 + rr.x, rr.y), bb = make_double2(1.0 - rr.x, -rr.y), ai = cinv(a);
+      d11[i] = cmul(make_double2(-bb.x, -bb.y), ai);
+      d12[i] = cscale(ai, 2.0);
+      d21[i] = cscale(csub(a, cmul(cmul(bb, ai), bb)), 0.5);
+      d22[i] = cmul(bb, ai);
     }
     __syncthreads();
     bool sing = false;
@@ -286,12 +389,12 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
       __syncthreads();
       // S_layer (smm_util.py:42-67)
       smm_axpby(T0, 1.0, A, 0.0, nullptr, 0.0, n, tid);
-      sing |= smm_inverse(Ai, T0, n, tid, slot);                  // A_i
+      sing |= smm_inverse(Ai, T0, n, tid, slot, fcol);            // A_i
       smm_gemm(T0, B, Ai, n, tid);
       smm_scale(T1, Xv, T0, Xv, n, tid);                          // T1 = X B A_i X
       smm_gemm(T2, T1, B, n, tid);
       smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - X B A_i X B
-      sing |= smm_inverse(T3, T2, n, tid, slot);                  // term_i
+      sing |= smm_inverse(T3, T2, n, tid, slot, fcol);            // term_i
       smm_gemm(T0, T1, A, n, tid);
       smm_axpby(T0, 1.0, T0, -1.0, B, 0.0, n, tid);
       smm_gemm(SL11, T3, T0, n, tid);                             // S11 = S22
@@ -302,32 +405,27 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
       smm_gemm(SL12, T3, T0, n, tid);                             // S12 = S21
       cplx* Lm[4] = {SL11, SL12, SL12, SL11};
       // Sg = Sg (*) S_layer   (scattering_1d_2)
-      if (cur == 0) { sing |= smm_redheffer(G, R, Lm, T0, T1, T2, T3, n, tid, slot); cur = 1; }
-      else if (cur == 1) { sing |= smm_redheffer(H, G, Lm, T0, T1, T2, T3, n, tid, slot); cur = 2; }
-      else { sing |= smm_redheffer(G, H, Lm, T0, T1, T2, T3, n, tid, slot); cur = 1; }
+      if (cur == 0) { sing |= smm_redheffer_diag_left(G, d11, d12, d21, d22, Lm, T0, T1, T2, T3, n, tid, slot, fcol); cur = 1; }
+      else if (cur == 1) { sing |= smm_redheffer(H, G, Lm, T0, T1, T2, T3, n, tid, slot, fcol); cur = 2; }
+      else { sing |= smm_redheffer(G, H, Lm, T0, T1, T2, T3, n, tid, slot, fcol); cur = 1; }
     }
-    // transmission region (ref_mode = False: blocks swapped)
-    for (int idx = tid; idx < n * n; idx += SMM_NT) {
-      const int i = idx / n, j = idx - i * n;
-      cplx s11 = make_double2(0, 0), s12 = s11, s21 = s11, s22 = s11;
-      if (i == j) {
-        const cplx rr = cmul(cinv(vg[i]), vt[i]);
-        const cplx a = make_double2(1.0 + rr.x, rr.y), bb = make_double2(1.0 - rr.x, -rr.y), ai = cinv(a);
-        s11 = cmul(make_double2(-bb.x, -bb.y), ai);
-        s12 = cscale(ai, 2.0);
-        s21 = cscale(csub(a, cmul(cmul(bb, ai), bb)), 0.5);
-        s22 = cmul(bb, ai);
-      }
-      R[0][idx] = s22; R[1][idx] = s21; R[2][idx] = s12; R[3][idx] = s11;
+    // transmission region (ref_mode = False: blocks swapped -> b11 = s22, b21 = s12); Sg = Sg (*) S_trn (scattering_1d_3), of
+    // which only column z (the incident harmonic) of S11 and S21 is used: rows {cos 1, sin 1, 0} = orders -1, +1, 0
+    for (int i = tid; i < n; i += SMM_NT) {
+      const cplx rr = cmul(cinv(vg[i]), vt[i]);
+      const cplx a = make_double2(1.0 + rr.x, rr.y), bb = make_double2(1.0 - rr.x, -rr.y), ai = cinv(a);
+      d11[i] = cmul(bb, ai);                                            // s22
+      d21[i] = cscale(ai, 2.0);                                         // s12
     }
     __syncthreads();
-    cplx* const* F;
-    if (cur == 1) { sing |= smm_redheffer(H, G, R, T0, T1, T2, T3, n, tid, slot); F = H; }     // Sg = Sg (*) S_trn  (scattering_1d_3)
-    else { sing |= smm_redheffer(G, H, R, T0, T1, T2, T3, n, tid, slot); F = G; }
+    cplx c11[3], c21[3];
+    const int rows[3] = {0, 1, z};
+    if (cur == 1) sing |= smm_redheffer_diag_right_col(c11, c21, rows, G, d11, d21, z, T0, T1, qv, Xv, d12, d22, n, tid, slot, fcol);
+    else sing |= smm_redheffer_diag_right_col(c11, c21, rows, H, d11, d21, z, T0, T1, qv, Xv, d12, d22, n, tid, slot, fcol);
     // fields of the incident zeroth order (c_inc = delta: W_r = I) and efficiencies of orders -1, 0, +1
     if (tid == 0) {
-      const cplx Rc = F[0][(size_t)0 * n + z], Rs = F[0][(size_t)1 * n + z], R0 = F[0][(size_t)z * n + z];
-      const cplx Tc = F[2][(size_t)0 * n + z], Ts = F[2][(size_t)1 * n + z], T0c = F[2][(size_t)z * n + z];
+      const cplx Rc = c11[0], Rs = c11[1], R0 = c11[2];
+      const cplx Tc = c21[0], Ts = c21[1], T0c = c21[2];
       const double is2 = 0.7071067811865476;
       const cplx Tm = make_double2((Tc.x - Ts.y) * is2, (Tc.y + Ts.x) * is2);
       const cplx Tp = make_double2((Tc.x + Ts.y) * is2, (Tc.y - Ts.x) * is2);
