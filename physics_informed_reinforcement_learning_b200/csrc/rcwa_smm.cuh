@@ -21,30 +21,82 @@ constexpr int SMM_NMAT = 17;          // complex ff x ff blocks of per-CTA scrat
 
 __host__ __device__ inline size_t smm_scratch_doubles(int ff) { return (size_t)SMM_NMAT * 2 * ff * ff + 2 * (size_t)ff * ff; }
 // shared: cre, cim [2N+1], per-harmonic complex diagonals vg, vr, vt, kzr, kzt, q, X, the four diagonal S-blocks of a half
-// space (d11, d12, d21, d22) and the pivot column of the inverse [ff each], pattern bits, pivot slot
-constexpr int SMM_NVEC = 12;
-__host__ __device__ inline int smm_smem_doubles(int ff, int N, int n_cells) {
-  return pirl_even(2 * (2 * N + 1)) + 2 * SMM_NVEC * ff + pirl_even((n_cells + 7) / 8) + 8;
+// space (d11, d12, d21, d22), the pivot column and the two pivot rows of the inverse [ff each], pattern bits, pivot slots,
+// row permutation, then the matrix region: GEMM panels (2 x ff x SMM_KC complex) and, when it fits, one ff x ff complex
+// matrix for the in-place inverse (the two share the region)
+constexpr int SMM_NVEC = 14;
+constexpr int SMM_KC = 16;            // GEMM panel depth
+constexpr int SMM_MAXB = 4;           // 2 x 2 output blocks per thread and row panel
+__host__ __device__ inline int smm_vec_doubles(int ff, int N, int n_cells) {
+  return pirl_even(2 * (2 * N + 1)) + 2 * SMM_NVEC * ff + pirl_even((n_cells + 7) / 8) + 32 + pirl_even(ff / 2 + 1);
+}
+__host__ __device__ inline int smm_panel_doubles(int ff) { return 2 * (2 * ff * SMM_KC); }
+// mats = 1: the region also holds the ff x ff complex matrix of the in-place inverse
+__host__ __device__ inline int smm_smem_doubles(int ff, int N, int n_cells, int mats) {
+  const int region = (mats && 2 * ff * ff > smm_panel_doubles(ff)) ? 2 * ff * ff : smm_panel_doubles(ff);
+  return smm_vec_doubles(ff, N, n_cells) + region;
 }
 
-// C = A B  (n x n complex, row major); each thread owns 2 x 2 output blocks
-__device__ __forceinline__ void smm_gemm(cplx* __restrict__ C, const cplx* __restrict__ A, const cplx* __restrict__ B, int n, int tid) {
-  const int nb = (n + 1) / 2;
-  for (int blk = tid; blk < nb * nb; blk += SMM_NT) {
-    const int i0 = 2 * (blk / nb), j0 = 2 * (blk % nb);
-    const bool i1 = i0 + 1 < n, j1 = j0 + 1 < n;
-    cplx c00 = make_double2(0, 0), c01 = c00, c10 = c00, c11 = c00;
-    const cplx* a0 = A + (size_t)i0 * n;
-    const cplx* a1 = A + (size_t)(i1 ? i0 + 1 : i0) * n;
-    for (int k = 0; k < n; ++k) {
-      const cplx x0 = a0[k], x1 = a1[k];
-      const cplx y0 = B[(size_t)k * n + j0], y1 = B[(size_t)k * n + (j1 ? j0 + 1 : j0)];
-      c00 = cfma(x0, y0, c00); c01 = cfma(x0, y1, c01);
-      c10 = cfma(x1, y0, c10); c11 = cfma(x1, y1, c11);
+// C = A B  (n x n complex, row major; C must not alias A or B).  Each thread owns up to SMM_MAXB 2 x 2 output blocks of a row
+// panel; A[panel rows, k0 : k0 + KC] and B[k0 : k0 + KC, :] are staged in shared memory (`tile`), so A is read from L2 once
+// and B once per row panel instead of once per output block.
+__device__ __noinline__ void smm_gemm(cplx* __restrict__ C, const cplx* __restrict__ A, const cplx* __restrict__ B, int n, int tid,
+                                         cplx* __restrict__ tile) {
+  const int nb = (n + 1) / 2;                                   // 2 x 2 blocks per row / column
+  int prow_b = (SMM_NT * SMM_MAXB) / nb;                        // block rows per panel
+  if (prow_b > nb) prow_b = nb;
+  const int prow = 2 * prow_b;                                  // matrix rows per panel
+  cplx* As = tile;                                              // [prow][KC]
+  cplx* Bs = tile + (size_t)((prow < n) ? prow : n) * SMM_KC;   // [KC][n]
+  for (int r0 = 0; r0 < n; r0 += prow) {
+    const int rows = (n - r0 < prow) ? n - r0 : prow;
+    const int nblk = ((rows + 1) / 2) * nb;
+    cplx acc[SMM_MAXB][4];
+#pragma unroll
+    for (int q = 0; q < SMM_MAXB; ++q) { acc[q][0] = acc[q][1] = acc[q][2] = acc[q][3] = make_double2(0, 0); }
+    for (int k0 = 0; k0 < n; k0 += SMM_KC) {
+      const int kc = (n - k0 < SMM_KC) ? n - k0 : SMM_KC;
+      __syncthreads();                                          // previous chunk consumed
+      for (int idx = tid; idx < rows * SMM_KC; idx += SMM_NT) {
+        const int i = idx / SMM_KC, kk = idx - i * SMM_KC;
+        As[idx] = (kk < kc) ? A[(size_t)(r0 + i) * n + k0 + kk] : make_double2(0, 0);
+      }
+      for (int idx = tid; idx < SMM_KC * n; idx += SMM_NT) {
+        const int kk = idx / n, j = idx - kk * n;
+        Bs[idx] = (kk < kc) ? B[(size_t)(k0 + kk) * n + j] : make_double2(0, 0);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int q = 0; q < SMM_MAXB; ++q) {
+        const int blk = tid + q * SMM_NT;
+        if (blk < nblk) {
+          const int bi = blk / nb, bj = blk - bi * nb;
+          const int i0 = 2 * bi, j0 = 2 * bj;
+          const cplx* a0 = As + (size_t)i0 * SMM_KC;
+          const cplx* a1 = As + (size_t)((i0 + 1 < rows) ? i0 + 1 : i0) * SMM_KC;
+          const int j1 = (j0 + 1 < n) ? j0 + 1 : j0;
+#pragma unroll
+          for (int kk = 0; kk < SMM_KC; ++kk) {
+            const cplx x0 = a0[kk], x1 = a1[kk];
+            const cplx y0 = Bs[kk * n + j0], y1 = Bs[kk * n + j1];
+            acc[q][0] = cfma(x0, y0, acc[q][0]); acc[q][1] = cfma(x0, y1, acc[q][1]);
+            acc[q][2] = cfma(x1, y0, acc[q][2]); acc[q][3] = cfma(x1, y1, acc[q][3]);
+          }
+        }
+      }
     }
-    C[(size_t)i0 * n + j0] = c00;
-    if (j1) C[(size_t)i0 * n + j0 + 1] = c01;
-    if (i1) { C[(size_t)(i0 + 1) * n + j0] = c10; if (j1) C[(size_t)(i0 + 1) * n + j0 + 1] = c11; }
+#pragma unroll
+    for (int q = 0; q < SMM_MAXB; ++q) {
+      const int blk = tid + q * SMM_NT;
+      if (blk < nblk) {
+        const int bi = blk / nb, bj = blk - bi * nb;
+        const int i0 = r0 + 2 * bi, j0 = 2 * bj;
+        const bool i1 = i0 + 1 < r0 + rows, j1 = j0 + 1 < n;
+        C[(size_t)i0 * n + j0] = acc[q][0];
+        if (j1) C[(size_t)i0 * n + j0 + 1] = acc[q][1];
+        if (i1) { C[(size_t)(i0 + 1) * n + j0] = acc[q][2]; if (j1) C[(size_t)(i0 + 1) * n + j0 + 1] = acc[q][3]; }
+      }
+    }
   }
   __syncthreads();
 }
@@ -95,7 +147,7 @@ __device__ __forceinline__ void smm_pivot_search(const cplx* __restrict__ A, int
 // One thread owns one COLUMN of [A | I] through a step (row swap, pivot-row scaling and elimination touch that column only), so
 // a step needs two barriers: the multipliers (column k) are staged in `fcol` first, and the owner of column k + 1 finds the
 // next pivot while it eliminates.  Rows are processed eight at a time, loads before stores, to keep eight L2 requests in flight.
-__device__ __forceinline__ bool smm_inverse(cplx* __restrict__ Ainv, cplx* __restrict__ A, int n, int tid, int* slot,
+__device__ __noinline__ bool smm_inverse(cplx* __restrict__ Ainv, cplx* __restrict__ A, int n, int tid, int* slot,
                                             cplx* __restrict__ fcol) {
   bool singular = false;
   for (int idx = tid; idx < n * n; idx += SMM_NT) Ainv[idx] = make_double2((idx / n == idx % n) ? 1.0 : 0.0, 0.0);
@@ -145,6 +197,90 @@ __device__ __forceinline__ bool smm_inverse(cplx* __restrict__ Ainv, cplx* __res
   return singular;
 }
 
+// Shared-memory work area of the inverse: multipliers, the two pivot rows, row permutation, pivot candidates
+struct SmmInvSm {
+  cplx* fcol; cplx* rowk; cplx* rowp; int* piv; double* candm; int* candi; int* slot;
+  cplx* Ms;            // ff x ff complex matrix in shared memory, or null (matrix stays in the L2-resident scratch)
+};
+
+// In-place Gauss-Jordan inverse with partial pivoting of the n x n complex matrix Ms in SHARED memory; the result (columns
+// permuted back) is written to the global Ainv.  Thread (g, c) owns rows i = g, g + G, ... of column c: every element is
+// read and written by one thread per step; the multipliers (column k) and the two rows that swap are staged first, and the
+// threads of column k + 1 leave pivot candidates for the next step.  Two barriers per step.
+__device__ __noinline__ bool smm_inverse_smem(cplx* __restrict__ Ainv, int n, int tid, const SmmInvSm& W) {
+  cplx* Ms = W.Ms;
+  int G = SMM_NT / n; if (G > 8) G = 8; if (G < 1) G = 1;
+  const int g = tid / n, c = tid - g * n;
+  const bool active = g < G;                 // (n <= SMM_NT is guaranteed by the plan when Ms is present)
+  bool singular = false;
+  if (tid < G) {                             // pivot candidates of column 0
+    double best = -1.0; int bi = 0;
+    for (int i = tid; i < n; i += G) { const cplx v = Ms[(size_t)i * n]; const double mg = fabs(v.x) + fabs(v.y); if (mg > best) { best = mg; bi = i; } }
+    W.candm[tid] = best; W.candi[tid] = bi;
+  }
+  __syncthreads();
+  for (int k = 0; k < n; ++k) {
+    double best = -1.0; int pv = k;
+    for (int q = 0; q < G; ++q) { const double m = W.candm[q]; const int i = W.candi[q]; if (m > best || (m == best && i < pv)) { best = m; pv = i; } }
+    if (!(best > 0.0)) pv = -1;
+    if (pv >= 0) {
+      for (int i = tid; i < n; i += SMM_NT) { W.fcol[i] = Ms[(size_t)i * n + k]; W.rowk[i] = Ms[(size_t)k * n + i]; W.rowp[i] = Ms[(size_t)pv * n + i]; }
+    }
+    if (tid == 0) W.piv[k] = (pv >= 0) ? pv : k;
+    __syncthreads();
+    if (pv < 0) {
+      singular = true;
+      if (tid < G) {
+        double b2 = -1.0; int bi = k + 1;
+        if (k + 1 < n) for (int i = k + 1 + tid; i < n; i += G) { const cplx v = Ms[(size_t)i * n + k + 1]; const double mg = fabs(v.x) + fabs(v.y); if (mg > b2) { b2 = mg; bi = i; } }
+        W.candm[tid] = b2; W.candi[tid] = bi;
+      }
+      __syncthreads();
+      continue;
+    }
+    if (active) {
+      const cplx pinv = cinv(W.fcol[pv]);
+      const cplx fswap = W.fcol[k];
+      const bool special = c == k;                     // column k of the in-place form: starts from the unit vector e_k
+      const cplx pk = special ? pinv : cmul(W.rowp[c], pinv);
+      const cplx a = W.rowk[c];                        // old row k: lands in row pv
+      const bool track = c == k + 1;
+      double tb = -1.0; int ti = k + 1;
+      for (int i = g; i < n; i += G) {
+        if (i == k) { Ms[(size_t)k * n + c] = pk; continue; }
+        cplx v = (i == pv) ? a : Ms[(size_t)i * n + c];
+        if (special) v = make_double2(0.0, 0.0);
+        const cplx r = cfnma((i == pv) ? fswap : W.fcol[i], pk, v);
+        Ms[(size_t)i * n + c] = r;
+        if (track && i > k) { const double mg = fabs(r.x) + fabs(r.y); if (mg > tb) { tb = mg; ti = i; } }
+      }
+      if (track) { W.candm[g] = tb; W.candi[g] = ti; }
+    }
+    __syncthreads();
+  }
+  // A^-1 = (P A)^-1 P: undo the row swaps as column swaps in reverse order, folded into one column map
+  int* src = reinterpret_cast<int*>(W.rowk);          // rowk is free now: n ints fit in n complex numbers
+  if (tid == 0) {
+    for (int j = 0; j < n; ++j) src[j] = j;
+    for (int k = n - 1; k >= 0; --k) { const int p2 = W.piv[k]; if (p2 != k) { const int t0 = src[k]; src[k] = src[p2]; src[p2] = t0; } }
+  }
+  __syncthreads();
+  for (int idx = tid; idx < n * n; idx += SMM_NT) {
+    const int i = idx / n, j = idx - i * n;
+    Ainv[idx] = Ms[(size_t)i * n + src[j]];
+  }
+  __syncthreads();
+  return singular;
+}
+
+// Ainv = A^-1 (A is destroyed): in shared memory when the plan found room for the matrix, else in the L2-resident scratch
+__device__ __forceinline__ bool smm_invert(cplx* __restrict__ Ainv, cplx* __restrict__ A, int n, int tid, const SmmInvSm& W) {
+  if (W.Ms == nullptr) return smm_inverse(Ainv, A, n, tid, W.slot, W.fcol);
+  for (int idx = tid; idx < n * n; idx += SMM_NT) W.Ms[idx] = A[idx];
+  __syncthreads();
+  return smm_inverse_smem(Ainv, n, tid, W);
+}
+
 // C = dl (.) A (.) dr (+ add) (+ diag(dg)): row scaling by dl, column scaling by dr (either may be null), optional addend and
 // diagonal
 __device__ __forceinline__ void smm_scale_add(cplx* C, const cplx* dl, const cplx* A, const cplx* dr, const cplx* add, const cplx* dg,
@@ -165,25 +301,25 @@ __device__ __forceinline__ void smm_scale_add(cplx* C, const cplx* dl, const cpl
 // Returns whether an inverse met a zero pivot.  The reference inverts both I - SB11 SA22 (D) and I - SA22 SB11 (F); here
 // F = I + SA22 D SB11 (push-through identity), one inverse per star product.
 __device__ __forceinline__ bool smm_redheffer(cplx* const (&O)[4], cplx* const (&SA)[4], cplx* const (&SB)[4], cplx* T0, cplx* T1,
-                                              cplx* T2, cplx* T3, int n, int tid, int* slot, cplx* fcol) {
+                                              cplx* T2, cplx* T3, int n, int tid, const SmmInvSm& W, cplx* tile) {
   bool sing = false;
-  smm_gemm(T0, SB[0], SA[3], n, tid);
+  smm_gemm(T0, SB[0], SA[3], n, tid, tile);
   smm_axpby(T0, -1.0, T0, 0.0, nullptr, 1.0, n, tid);
-  sing |= smm_inverse(T1, T0, n, tid, slot, fcol);             // T1 = D = inv(I - SB11 SA22)
-  smm_gemm(T2, T1, SB[0], n, tid);                             // T2 = D SB11
-  smm_gemm(T3, T1, SB[1], n, tid);                             // T3 = D SB12
+  sing |= smm_invert(T1, T0, n, tid, W);             // T1 = D = inv(I - SB11 SA22)
+  smm_gemm(T2, T1, SB[0], n, tid, tile);                             // T2 = D SB11
+  smm_gemm(T3, T1, SB[1], n, tid, tile);                             // T3 = D SB12
   // S12 = SA12 D SB12 ; S11 = SA11 + SA12 D SB11 SA21
-  smm_gemm(O[1], SA[1], T3, n, tid);
-  smm_gemm(T0, SA[1], T2, n, tid);
-  smm_gemm(T1, T0, SA[2], n, tid);
+  smm_gemm(O[1], SA[1], T3, n, tid, tile);
+  smm_gemm(T0, SA[1], T2, n, tid, tile);
+  smm_gemm(T1, T0, SA[2], n, tid, tile);
   smm_axpby(O[0], 1.0, SA[0], 1.0, T1, 0.0, n, tid);
   // F = I + SA22 D SB11 ; S21 = SB21 F SA21 ; S22 = SB22 + SB21 F SA22 SB12
-  smm_gemm(T0, SA[3], T2, n, tid);
+  smm_gemm(T0, SA[3], T2, n, tid, tile);
   smm_axpby(T0, 1.0, T0, 0.0, nullptr, 1.0, n, tid);           // T0 = F
-  smm_gemm(T1, SB[2], T0, n, tid);                             // T1 = SB21 F
-  smm_gemm(O[2], T1, SA[2], n, tid);
-  smm_gemm(T3, T1, SA[3], n, tid);
-  smm_gemm(T0, T3, SB[1], n, tid);
+  smm_gemm(T1, SB[2], T0, n, tid, tile);                             // T1 = SB21 F
+  smm_gemm(O[2], T1, SA[2], n, tid, tile);
+  smm_gemm(T3, T1, SA[3], n, tid, tile);
+  smm_gemm(T0, T3, SB[1], n, tid, tile);
   smm_axpby(O[3], 1.0, SB[3], 1.0, T0, 0.0, n, tid);
   return sing;
 }
@@ -192,16 +328,16 @@ __device__ __forceinline__ bool smm_redheffer(cplx* const (&O)[4], cplx* const (
 // diagonals.  Products with a diagonal block are scalings: four GEMMs and one inverse.
 __device__ __forceinline__ bool smm_redheffer_diag_left(cplx* const (&O)[4], const cplx* a11, const cplx* a12, const cplx* a21,
                                                         const cplx* a22, cplx* const (&SB)[4], cplx* T0, cplx* T1, cplx* T2, cplx* T3,
-                                                        int n, int tid, int* slot, cplx* fcol) {
+                                                        int n, int tid, const SmmInvSm& W, cplx* tile) {
   for (int idx = tid; idx < n * n; idx += SMM_NT) {           // T0 = I - SB11 a22
     const int i = idx / n, j = idx - i * n;
     const cplx v = cmul(SB[0][idx], a22[j]);
     T0[idx] = make_double2(((i == j) ? 1.0 : 0.0) - v.x, -v.y);
   }
   __syncthreads();
-  const bool sing = smm_inverse(T1, T0, n, tid, slot, fcol);  // T1 = D
-  smm_gemm(T2, T1, SB[0], n, tid);                             // T2 = D SB11
-  smm_gemm(T3, T1, SB[1], n, tid);                             // T3 = D SB12
+  const bool sing = smm_invert(T1, T0, n, tid, W);  // T1 = D
+  smm_gemm(T2, T1, SB[0], n, tid, tile);                             // T2 = D SB11
+  smm_gemm(T3, T1, SB[1], n, tid, tile);                             // T3 = D SB12
   smm_scale_add(O[0], a12, T2, a21, nullptr, a11, n, tid);     // S11 = a11 + a12 D SB11 a21
   smm_scale_add(O[1], a12, T3, nullptr, nullptr, nullptr, n, tid);   // S12 = a12 D SB12
   for (int idx = tid; idx < n * n; idx += SMM_NT) {           // T0 = F = I + a22 D SB11
@@ -210,10 +346,10 @@ __device__ __forceinline__ bool smm_redheffer_diag_left(cplx* const (&O)[4], con
     T0[idx] = make_double2(((i == j) ? 1.0 : 0.0) + v.x, v.y);
   }
   __syncthreads();
-  smm_gemm(T1, SB[2], T0, n, tid);                             // T1 = SB21 F
+  smm_gemm(T1, SB[2], T0, n, tid, tile);                             // T1 = SB21 F
   smm_scale_add(O[2], nullptr, T1, a21, nullptr, nullptr, n, tid);   // S21 = SB21 F a21
   smm_scale_add(T0, nullptr, T1, a22, nullptr, nullptr, n, tid);     // T0 = SB21 F a22
-  smm_gemm(T2, T0, SB[1], n, tid);
+  smm_gemm(T2, T0, SB[1], n, tid, tile);
   smm_axpby(O[3], 1.0, SB[3], 1.0, T2, 0.0, n, tid);           // S22 = SB22 + SB21 F a22 SB12
   return sing;
 }
@@ -225,7 +361,7 @@ __device__ __forceinline__ bool smm_redheffer_diag_left(cplx* const (&O)[4], con
 // as 3); results for `rows[0..3)` only.
 __device__ __forceinline__ bool smm_redheffer_diag_right_col(cplx (&s11)[3], cplx (&s21)[3], const int (&rows)[3], cplx* const (&SA)[4],
                                                              const cplx* b11, const cplx* b21, int z, cplx* T0, cplx* T1, cplx* u,
-                                                             cplx* v, cplx* pa, cplx* pb, int n, int tid, int* slot, cplx* fcol) {
+                                                             cplx* v, cplx* pa, cplx* pb, int n, int tid, const SmmInvSm& W, cplx* tile) {
   for (int idx = tid; idx < n * n; idx += SMM_NT) {           // T0 = I - b11 SA22
     const int i = idx / n, j = idx - i * n;
     const cplx w = cmul(b11[i], SA[3][idx]);
@@ -233,7 +369,7 @@ __device__ __forceinline__ bool smm_redheffer_diag_right_col(cplx (&s11)[3], cpl
   }
   for (int i = tid; i < n; i += SMM_NT) u[i] = cmul(b11[i], SA[2][(size_t)i * n + z]);
   __syncthreads();
-  const bool sing = smm_inverse(T1, T0, n, tid, slot, fcol);  // T1 = D
+  const bool sing = smm_invert(T1, T0, n, tid, W);  // T1 = D
   const int lane = tid & 31, warp = tid >> 5;
   for (int i = warp; i < n; i += SMM_NT / 32) {                // v = D u, one warp per row
     cplx acc = make_double2(0, 0);
@@ -295,9 +431,17 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
   cplx* d12 = d11 + ff;
   cplx* d21 = d12 + ff;
   cplx* d22 = d21 + ff;
-  cplx* fcol = d22 + ff;               // pivot column of smm_inverse
-  uint8_t* su = reinterpret_cast<uint8_t*>(fcol + ff);
-  int* slot = reinterpret_cast<int*>(su + 8 * pirl_even((nc + 7) / 8));
+  cplx* fcol = d22 + ff;               // pivot column of the inverse
+  cplx* rowk = fcol + ff;              // the two rows that swap in a step of the in-place inverse
+  cplx* rowp = rowk + ff;
+  uint8_t* su = reinterpret_cast<uint8_t*>(rowp + ff);
+  double* misc = reinterpret_cast<double*>(su + 8 * pirl_even((nc + 7) / 8));      // [32]: pivot slot and candidates
+  int* slot = reinterpret_cast<int*>(misc);
+  cplx* tile = reinterpret_cast<cplx*>(sm + smm_vec_doubles(ff, N, nc));           // GEMM panels / matrix of the inverse
+  SmmInvSm W;
+  W.fcol = fcol; W.rowk = rowk; W.rowp = rowp; W.slot = slot; W.candm = misc + 8; W.candi = reinterpret_cast<int*>(misc + 16);
+  W.piv = reinterpret_cast<int*>(misc + 32);
+  W.Ms = P.smem_mats ? tile : nullptr;
   cplx* base = reinterpret_cast<cplx*>(smm_scratch + (size_t)blockIdx.x * smm_scratch_doubles(ff));
   const size_t m2 = (size_t)n * n;
   cplx* M[SMM_NMAT];
@@ -389,25 +533,25 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
       __syncthreads();
       // S_layer (smm_util.py:42-67)
       smm_axpby(T0, 1.0, A, 0.0, nullptr, 0.0, n, tid);
-      sing |= smm_inverse(Ai, T0, n, tid, slot, fcol);            // A_i
-      smm_gemm(T0, B, Ai, n, tid);
+      sing |= smm_invert(Ai, T0, n, tid, W);            // A_i
+      smm_gemm(T0, B, Ai, n, tid, tile);
       smm_scale(T1, Xv, T0, Xv, n, tid);                          // T1 = X B A_i X
-      smm_gemm(T2, T1, B, n, tid);
+      smm_gemm(T2, T1, B, n, tid, tile);
       smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - X B A_i X B
-      sing |= smm_inverse(T3, T2, n, tid, slot, fcol);            // term_i
-      smm_gemm(T0, T1, A, n, tid);
+      sing |= smm_invert(T3, T2, n, tid, W);            // term_i
+      smm_gemm(T0, T1, A, n, tid, tile);
       smm_axpby(T0, 1.0, T0, -1.0, B, 0.0, n, tid);
-      smm_gemm(SL11, T3, T0, n, tid);                             // S11 = S22
-      smm_gemm(T0, Ai, B, n, tid);
-      smm_gemm(T2, B, T0, n, tid);
+      smm_gemm(SL11, T3, T0, n, tid, tile);                             // S11 = S22
+      smm_gemm(T0, Ai, B, n, tid, tile);
+      smm_gemm(T2, B, T0, n, tid, tile);
       smm_axpby(T2, 1.0, A, -1.0, T2, 0.0, n, tid);               // A - B A_i B
       smm_scale(T0, Xv, T2, nullptr, n, tid);
-      smm_gemm(SL12, T3, T0, n, tid);                             // S12 = S21
+      smm_gemm(SL12, T3, T0, n, tid, tile);                             // S12 = S21
       cplx* Lm[4] = {SL11, SL12, SL12, SL11};
       // Sg = Sg (*) S_layer   (scattering_1d_2)
-      if (cur == 0) { sing |= smm_redheffer_diag_left(G, d11, d12, d21, d22, Lm, T0, T1, T2, T3, n, tid, slot, fcol); cur = 1; }
-      else if (cur == 1) { sing |= smm_redheffer(H, G, Lm, T0, T1, T2, T3, n, tid, slot, fcol); cur = 2; }
-      else { sing |= smm_redheffer(G, H, Lm, T0, T1, T2, T3, n, tid, slot, fcol); cur = 1; }
+      if (cur == 0) { sing |= smm_redheffer_diag_left(G, d11, d12, d21, d22, Lm, T0, T1, T2, T3, n, tid, W, tile); cur = 1; }
+      else if (cur == 1) { sing |= smm_redheffer(H, G, Lm, T0, T1, T2, T3, n, tid, W, tile); cur = 2; }
+      else { sing |= smm_redheffer(G, H, Lm, T0, T1, T2, T3, n, tid, W, tile); cur = 1; }
     }
     // transmission region (ref_mode = False: blocks swapped -> b11 = s22, b21 = s12); Sg = Sg (*) S_trn (scattering_1d_3), of
     // which only column z (the incident harmonic) of S11 and S21 is used: rows {cos 1, sin 1, 0} = orders -1, +1, 0
@@ -420,8 +564,8 @@ __global__ void __launch_bounds__(SMM_NT) k_smm(KParams P, double* __restrict__ 
     __syncthreads();
     cplx c11[3], c21[3];
     const int rows[3] = {0, 1, z};
-    if (cur == 1) sing |= smm_redheffer_diag_right_col(c11, c21, rows, G, d11, d21, z, T0, T1, qv, Xv, d12, d22, n, tid, slot, fcol);
-    else sing |= smm_redheffer_diag_right_col(c11, c21, rows, H, d11, d21, z, T0, T1, qv, Xv, d12, d22, n, tid, slot, fcol);
+    if (cur == 1) sing |= smm_redheffer_diag_right_col(c11, c21, rows, G, d11, d21, z, T0, T1, qv, Xv, d12, d22, n, tid, W, tile);
+    else sing |= smm_redheffer_diag_right_col(c11, c21, rows, H, d11, d21, z, T0, T1, qv, Xv, d12, d22, n, tid, W, tile);
     // fields of the incident zeroth order (c_inc = delta: W_r = I) and efficiencies of orders -1, 0, +1
     if (tid == 0) {
       const cplx Rc = c11[0], Rs = c11[1], R0 = c11[2];

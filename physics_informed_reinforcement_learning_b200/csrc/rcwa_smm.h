@@ -6,6 +6,7 @@ struct SmmPlan {
   bool ok = false;
   int grid = 0;                    // persistent CTAs (each with its own scratch)
   size_t smem = 0;
+  int mats = 0;                    // 1: the matrix of the in-place inverse lives in shared memory
   size_t scratch_doubles = 0;      // per CTA
 };
 
